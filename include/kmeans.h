@@ -1,0 +1,175 @@
+/*
+ * kmeans.h — C ABI of libkmeans.so: the Lloyd iteration (initialisation, assignment,
+ * centroid update, run-to-convergence) on NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the one path BASELINE.json's north_star names.  The
+ * reference (schusto/k-means-demo) has no FFI, no `export` and no numerical Lloyd code
+ * (SURVEY.md §0 F1, §8b); each entry point below therefore cites the *manual analog* in
+ * /root/reference/app.mjs that it stands in for, and the semantics are SURVEY.md
+ * Appendix A ("OUR SPEC").  A maintainer binds these from the JS side through an N-API
+ * addon (INTEGRATION.md shows the stub); every buffer is a plain pointer + size that maps
+ * 1:1 onto a Float32Array / Float64Array / Int32Array / BigInt64Array backing store.
+ *
+ * Conventions
+ *   - every call returns km_status (0 = OK, negative = error); text via km_last_error().
+ *     Nothing throws or aborts across the boundary.
+ *   - host pointers passed in are borrowed for the duration of the call only; results are
+ *     copied into caller-allocated buffers.  The library owns all device and pinned memory.
+ *   - one km_ctx = one GPU = one owner thread at a time.  Multi-GPU = one ctx per process
+ *     per GPU, joined with km_comm_init() (NCCL over NVLink/NVSwitch).
+ *   - there is no CPU fallback: without a usable CUDA device km_create() fails.
+ */
+#ifndef KMEANS_B200_H
+#define KMEANS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KM_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define KM_API __attribute__((visibility("default")))
+#else
+#define KM_API
+#endif
+
+typedef struct km_ctx km_ctx;
+typedef int32_t km_status;
+
+enum {
+  KM_OK = 0,
+  KM_ERR_INVALID_ARG = -1,
+  KM_ERR_CUDA = -2,
+  KM_ERR_NCCL = -3,
+  KM_ERR_OOM = -4,
+  KM_ERR_STATE = -5,      /* call made in the wrong order (no points, no centroids, ...) */
+  KM_ERR_NONFINITE = -6,  /* NaN / Inf among the points or centroids */
+  KM_ERR_UNSUPPORTED = -7
+};
+
+/* storage type of the points handed to km_upload_points / km_attach_points */
+enum { KM_DTYPE_F32 = 0, KM_DTYPE_F64 = 1 };
+
+/* which assignment kernel family runs (km_config.path) */
+enum {
+  KM_PATH_AUTO = 0,       /* pick by (d, k) */
+  KM_PATH_DIRECT_F64 = 1, /* every distance in binary64, the oracle's exact op order */
+  KM_PATH_FILTER_F32 = 2, /* binary32 distances + error-bound test + binary64 re-score */
+  KM_PATH_TENSOR = 3      /* tcgen05 GEMM-form distances + error-bound test + re-score */
+};
+
+/* how the per-cluster sums are maintained (results are bit-identical either way) */
+enum {
+  KM_UPDATE_INCREMENTAL = 0, /* only points whose label changed move between sums */
+  KM_UPDATE_FULL = 1         /* every point is re-accumulated every iteration */
+};
+
+typedef struct km_config {
+  int32_t struct_size; /* = sizeof(km_config); ABI guard */
+  int32_t device;      /* CUDA ordinal */
+  int32_t path;        /* KM_PATH_* */
+  int32_t update_mode; /* KM_UPDATE_* */
+  int32_t exact_inertia; /* 1: inertia from binary64 winner distances (<=1e-9 rel);
+                            0: from the filter's binary32 distances (<=1e-5 rel) */
+  int32_t reserved0;
+  void *stream;        /* cudaStream_t to run on, or NULL for a private stream */
+} km_config;
+
+typedef struct km_stats {
+  int32_t iterations;  /* assign steps executed since the labels were last reset */
+  int32_t converged;   /* 1 when the last assign changed no label */
+  int64_t changed;     /* labels changed by the last assign (whole job, all ranks) */
+  double inertia;      /* sum of winner distances of the last assign (whole job) */
+  int64_t rescored;    /* points the last assign re-scored in binary64 (whole job) */
+  int64_t n_total;     /* points in the whole job */
+  float device_ms;     /* device time of this call, CUDA events on the ctx stream */
+  int32_t path_used;   /* KM_PATH_* the last assign actually ran */
+} km_stats;
+
+/* ---- life cycle ------------------------------------------------------------------ */
+KM_API int32_t km_abi_version(void);
+/* replaces: nothing — the reference keeps its state in module-scope Yjs globals
+ * (app.mjs:29-33).  A ctx is that state made explicit. */
+KM_API km_status km_create(const km_config *cfg, km_ctx **out);
+KM_API km_status km_destroy(km_ctx *ctx);
+/* last error text of `ctx` (or of the calling thread's last failed km_create if NULL) */
+KM_API const char *km_last_error(const km_ctx *ctx);
+
+/* page-locked host memory for callers that want km_upload_points / km_get_* to copy
+ * straight from / into their buffer (an N-API host wraps it in an external ArrayBuffer) */
+KM_API km_status km_host_alloc(void **out, uint64_t bytes);
+KM_API km_status km_host_free(void *p);
+
+/* ---- multi-GPU (one process per GPU) -------------------------------- */
+/* 128-byte NCCL unique id: rank 0 produces it, the host layer broadcasts it */
+KM_API km_status km_comm_unique_id(void *out128);
+/* join a communicator of `world` ranks.  Must precede km_upload_points/km_generate_blobs.
+ * replaces: the P2PT/WebRTC gossip of UI state (app.mjs:70-118) only in the sense that it
+ * is the reference's sole inter-process link; it is not a compute collective there. */
+KM_API km_status km_comm_init(km_ctx *ctx, const void *id128, int32_t rank, int32_t world);
+
+/* ---- a1: point / centroid store (analog: cards app.mjs:31,143-145; centroids :32,128) */
+/* copy this rank's shard (n x d, row-major) from host memory through pinned staging.
+ * Also scans for NaN/Inf and max|x| (needed by the order-free sums). */
+KM_API km_status km_upload_points(km_ctx *ctx, const void *host, int64_t n, int32_t d, int32_t dtype);
+/* use points already resident in device memory (borrowed; must outlive the ctx's use) */
+KM_API km_status km_attach_points(km_ctx *ctx, const void *device, int64_t n, int32_t d, int32_t dtype);
+/* device-side seeded blob generator: rows [i0, i0+n) of the job's matrix */
+KM_API km_status km_generate_blobs(km_ctx *ctx, int64_t n, int64_t i0, int32_t d, int32_t k_true,
+                            uint64_t seed, double sigma);
+/* copy rows [i0, i0+n) of this rank's shard back to the host (float32 or float64 as stored) */
+KM_API km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t n);
+
+/* ---- a2: initialisation (analog: addCentroid app.mjs:126-129; shuffle idiom :163) --- */
+KM_API km_status km_set_centroids(km_ctx *ctx, const double *c, int32_t k);
+/* seeded Forgy: first k picks of a partial Fisher-Yates over the job's point indices */
+KM_API km_status km_init_forgy(km_ctx *ctx, int32_t k, uint64_t seed);
+
+/* ---- a3: assignment step (analog: updateCardAssign app.mjs:146-156, drop :358-372) -- */
+/* label[i] = argmin_j sum_t (x_it - c_jt)^2, strict <, lowest j wins ties; also counts
+ * changed labels, sums the winner distances, and moves each re-labelled point between the
+ * per-cluster sums (the update's partial sums are fused into this pass). */
+KM_API km_status km_assign(km_ctx *ctx, km_stats *stats);
+
+/* ---- a4: centroid-update step (analog: traitCountsFor/suggestionFromCounts/
+ *          applySuggestedName app.mjs:450-461,476-480,571-573; counts :485-486) -------- */
+/* c_j = sum_j / count_j; an empty cluster keeps its centroid (app.mjs:322,484-488) */
+KM_API km_status km_update(km_ctx *ctx, km_stats *stats);
+
+/* one Lloyd iteration: assign; update unless nothing changed */
+KM_API km_status km_step(km_ctx *ctx, km_stats *stats);
+/* same, enqueued without waiting for the device; read results with km_stats_fetch */
+KM_API km_status km_step_async(km_ctx *ctx);
+KM_API km_status km_stats_fetch(km_ctx *ctx, km_stats *stats);
+
+/* ---- a5: run to convergence (analog: #iter -> yMeta.iteration app.mjs:286-288,498-508) */
+/* labels reset to -1; repeat { assign; it++; if (changed==0 || it==max_iter) break; update } */
+KM_API km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats);
+/* forget labels and sums (the next assign sees every label as changed) */
+KM_API km_status km_reset_labels(km_ctx *ctx);
+
+/* ---- results ----------------------------------------------------------------------- */
+KM_API km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n);   /* this rank's shard */
+KM_API km_status km_get_centroids(km_ctx *ctx, double *out);            /* k*d, row-major */
+/* a6: per-cluster member counts of the whole job (analog: snapshotMetrics counts
+ * app.mjs:481-496) */
+KM_API km_status km_get_counts(km_ctx *ctx, int64_t *out);
+/* a6: balance{max,min,gap,ratio} with the reference's formulas (app.mjs:489-493):
+ * ratio = min ? max/min : (max ? Infinity : 1) */
+KM_API km_status km_get_balance(km_ctx *ctx, int64_t *max_out, int64_t *min_out, int64_t *gap_out,
+                         double *ratio_out);
+/* raw order-free sums of the whole job: k*d `a` limbs, k*d `b` limbs, then the fixed-point
+ * parameters {E, NB, QB, qa} (for bit-level parity tests) */
+KM_API km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t params4[4]);
+
+KM_API km_status km_sync(km_ctx *ctx);
+/* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
+KM_API int64_t km_launch_count(const km_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMEANS_B200_H */

@@ -1,0 +1,812 @@
+// km_api.cu — the C ABI of libkmeans.so (include/kmeans.h): context, point/centroid
+// store, Lloyd driver loop, NCCL plumbing.  No CPU fallback anywhere: every compute
+// entry point enqueues CUDA kernels or fails.
+#include <dlfcn.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "km_internal.h"
+
+// ------------------------------------------------------------------ errors
+static thread_local std::string g_create_err;
+
+static km_status fail(km_ctx *ctx, km_status code, const std::string &msg) {
+  if (ctx) ctx->err = msg; else g_create_err = msg;
+  return code;
+}
+#define KM_CUDA(ctx, expr)                                                                      \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      return fail(ctx, _e == cudaErrorMemoryAllocation ? KM_ERR_OOM : KM_ERR_CUDA,              \
+                  std::string(#expr) + ": " + cudaGetErrorString(_e));                          \
+    }                                                                                           \
+  } while (0)
+
+// ------------------------------------------------------------------ NCCL, loaded lazily
+// Nothing links against NCCL: single-GPU users never need it, and a process that already
+// carries an NCCL (e.g. a Python host with torch) shares that copy through the SONAME.
+struct KmNcclUniqueId { char internal[128]; };
+typedef int (*nccl_get_unique_id_t)(KmNcclUniqueId *);
+typedef int (*nccl_comm_init_rank_t)(void **, int, KmNcclUniqueId, int);
+typedef int (*nccl_comm_destroy_t)(void *);
+typedef int (*nccl_all_reduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*nccl_all_gather_t)(const void *, void *, size_t, int, void *, cudaStream_t);
+typedef const char *(*nccl_get_error_string_t)(int);
+enum { KM_NCCL_INT64 = 4, KM_NCCL_FLOAT64 = 8, KM_NCCL_SUM = 0, KM_NCCL_MAX = 2 };
+
+static struct {
+  void *handle = nullptr;
+  nccl_get_unique_id_t get_unique_id = nullptr;
+  nccl_comm_init_rank_t comm_init_rank = nullptr;
+  nccl_comm_destroy_t comm_destroy = nullptr;
+  nccl_all_reduce_t all_reduce = nullptr;
+  nccl_all_gather_t all_gather = nullptr;
+  nccl_get_error_string_t get_error_string = nullptr;
+} g_nccl;
+
+static bool nccl_load(std::string &why) {
+  if (g_nccl.handle) return true;
+  void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) { why = std::string("dlopen libnccl.so.2: ") + dlerror(); return false; }
+  g_nccl.get_unique_id = (nccl_get_unique_id_t)dlsym(h, "ncclGetUniqueId");
+  g_nccl.comm_init_rank = (nccl_comm_init_rank_t)dlsym(h, "ncclCommInitRank");
+  g_nccl.comm_destroy = (nccl_comm_destroy_t)dlsym(h, "ncclCommDestroy");
+  g_nccl.all_reduce = (nccl_all_reduce_t)dlsym(h, "ncclAllReduce");
+  g_nccl.all_gather = (nccl_all_gather_t)dlsym(h, "ncclAllGather");
+  g_nccl.get_error_string = (nccl_get_error_string_t)dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.comm_destroy || !g_nccl.all_reduce ||
+      !g_nccl.all_gather || !g_nccl.get_error_string) {
+    why = "libnccl.so.2 lacks an expected symbol";
+    return false;
+  }
+  g_nccl.handle = h;
+  return true;
+}
+#define KM_NCCL(ctx, expr)                                                                       \
+  do {                                                                                           \
+    int _r = (expr);                                                                             \
+    if (_r != 0) return fail(ctx, KM_ERR_NCCL, std::string(#expr) + ": " + g_nccl.get_error_string(_r)); \
+  } while (0)
+
+// ------------------------------------------------------------------ helpers
+static size_t elt_size(int dtype) { return dtype == KM_DTYPE_F32 ? sizeof(float) : sizeof(double); }
+
+static km_status bind(km_ctx *ctx) {
+  if (!ctx) return KM_ERR_INVALID_ARG;
+  KM_CUDA(ctx, cudaSetDevice(ctx->device));
+  return KM_OK;
+}
+#define KM_BIND(ctx)                         \
+  do {                                       \
+    km_status _s = bind(ctx);                \
+    if (_s != KM_OK) return _s;              \
+  } while (0)
+
+static void free_points(km_ctx *ctx) {
+  if (ctx->x && ctx->own_x) cudaFree(ctx->x);
+  if (ctx->labels) cudaFree(ctx->labels);
+  ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
+  ctx->n = 0; ctx->n_total = 0; ctx->i0 = 0;
+}
+static void free_centroids(km_ctx *ctx) {
+  if (ctx->c64) cudaFree(ctx->c64);
+  if (ctx->chi) cudaFree(ctx->chi);
+  if (ctx->clo) cudaFree(ctx->clo);
+  if (ctx->acc_global && ctx->acc_global != ctx->acc) cudaFree(ctx->acc_global);
+  if (ctx->acc) cudaFree(ctx->acc);
+  ctx->c64 = nullptr; ctx->chi = ctx->clo = nullptr; ctx->acc = ctx->acc_global = nullptr;
+  ctx->have_centroids = false; ctx->k = 0; ctx->acc_len = 0;
+}
+
+static km_status ensure_pinned(km_ctx *ctx, size_t bytes) {
+  if (ctx->pinned_bytes >= bytes) return KM_OK;
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  ctx->pinned = nullptr; ctx->pinned_bytes = 0;
+  KM_CUDA(ctx, cudaHostAlloc(&ctx->pinned, bytes, cudaHostAllocDefault));
+  ctx->pinned_bytes = bytes;
+  return KM_OK;
+}
+
+static bool is_pinned_host(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// host -> device through pinned staging (two halves in flight), or directly when the
+// caller's buffer is already page-locked
+static km_status copy_h2d(km_ctx *ctx, void *dst, const void *src, size_t bytes) {
+  if (bytes == 0) return KM_OK;
+  if (is_pinned_host(src)) {
+    KM_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return KM_OK;
+  }
+  const size_t half = 32u << 20;
+  km_status s = ensure_pinned(ctx, 2 * half);
+  if (s != KM_OK) return s;
+  cudaEvent_t done[2];
+  KM_CUDA(ctx, cudaEventCreateWithFlags(&done[0], cudaEventDisableTiming));
+  KM_CUDA(ctx, cudaEventCreateWithFlags(&done[1], cudaEventDisableTiming));
+  size_t off = 0;
+  int slot = 0;
+  bool used[2] = {false, false};
+  cudaError_t e = cudaSuccess;
+  while (off < bytes && e == cudaSuccess) {
+    size_t len = std::min(half, bytes - off);
+    char *stage = (char *)ctx->pinned + (size_t)slot * half;
+    if (used[slot]) e = cudaEventSynchronize(done[slot]);
+    if (e != cudaSuccess) break;
+    memcpy(stage, (const char *)src + off, len);
+    e = cudaMemcpyAsync((char *)dst + off, stage, len, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(done[slot], ctx->stream);
+    used[slot] = true;
+    off += len;
+    slot ^= 1;
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaEventDestroy(done[0]);
+  cudaEventDestroy(done[1]);
+  KM_CUDA(ctx, e);
+  return KM_OK;
+}
+
+static km_status copy_d2h(km_ctx *ctx, void *dst, const void *src, size_t bytes) {
+  if (bytes == 0) return KM_OK;
+  if (is_pinned_host(dst)) {
+    KM_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return KM_OK;
+  }
+  const size_t chunk = 32u << 20;
+  km_status s = ensure_pinned(ctx, 2 * chunk);
+  if (s != KM_OK) return s;
+  size_t off = 0;
+  while (off < bytes) {
+    size_t len = std::min(chunk, bytes - off);
+    KM_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, (const char *)src + off, len, cudaMemcpyDeviceToHost, ctx->stream));
+    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memcpy((char *)dst + off, ctx->pinned, len);
+    off += len;
+  }
+  return KM_OK;
+}
+
+static int bitlen64(int64_t v) { int b = 1; while (b < 62 && ((int64_t)1 << b) <= v) b++; return b; }
+
+// fixed-point parameters of the order-free sums from the job's max|x| and N
+static km_status push_state(km_ctx *ctx) {
+  int E = 0;
+  if (ctx->maxabs > 0.0) E = ilogb(ctx->maxabs) + 1;
+  int NB = bitlen64(ctx->n_total);
+  ctx->E = E; ctx->NB = NB; ctx->QB = 62 - NB; ctx->qa = ctx->QB - E;
+  KmState st;
+  memset(&st, 0, sizeof(st));
+  st.QB = ctx->QB; st.qa = ctx->qa; st.E = E;
+  st.scale_a = ldexp(1.0, ctx->qa);
+  st.scale_b = ldexp(1.0, ctx->QB);
+  st.qi = ctx->QB;  // refreshed with the centroids
+  st.inertia_scale = ldexp(1.0, st.qi);
+  KM_CUDA(ctx, cudaMemcpyAsync(ctx->state, &st, sizeof(st), cudaMemcpyHostToDevice, ctx->stream));
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
+static km_status reset_labels(km_ctx *ctx) {
+  if (ctx->labels) KM_CUDA(ctx, km_launch_fill_i32(ctx->labels, ctx->n, -1, ctx->sm_count, ctx->stream, &ctx->launches));
+  if (ctx->acc) KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
+  if (ctx->acc_global && ctx->acc_global != ctx->acc)
+    KM_CUDA(ctx, cudaMemsetAsync(ctx->acc_global, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
+  if (ctx->state) KM_CUDA(ctx, cudaMemsetAsync(&ctx->state->it, 0, sizeof(int32_t), ctx->stream));
+  ctx->host_it = 0;
+  ctx->labels_fresh = true;
+  return KM_OK;
+}
+
+// after the shard is on the device: scan it, agree on the job-wide scale, reset labels
+static km_status adopt_points(km_ctx *ctx) {
+  double *d_max = nullptr;
+  int *d_bad = nullptr;
+  KM_CUDA(ctx, cudaMalloc(&d_max, sizeof(double)));
+  KM_CUDA(ctx, cudaMalloc(&d_bad, sizeof(int)));
+  cudaError_t e = km_launch_scan(ctx->x, ctx->dtype, ctx->n * (int64_t)ctx->d, d_max, d_bad, ctx->sm_count, ctx->stream,
+                                 &ctx->launches);
+  double hmax = 0.0;
+  int hbad = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&hmax, d_max, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&hbad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  int64_t n_total = ctx->n, i0 = 0;
+  if (e == cudaSuccess && ctx->world > 1) {
+    // job-wide: max of max|x|, any non-finite, shard offsets — one all-gather of 3 doubles
+    double *d_in = nullptr, *d_out = nullptr;
+    e = cudaMalloc(&d_in, 3 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, 3 * sizeof(double) * ctx->world);
+    double h_in[3] = {hmax, (double)hbad, (double)ctx->n};
+    std::vector<double> h_out(3 * (size_t)ctx->world);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, ctx->stream);
+    int r = 0;
+    if (e == cudaSuccess) r = g_nccl.all_gather(d_in, d_out, 3, KM_NCCL_FLOAT64, ctx->nccl_comm, ctx->stream);
+    if (e == cudaSuccess && r == 0)
+      e = cudaMemcpyAsync(h_out.data(), d_out, h_out.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && r == 0) e = cudaStreamSynchronize(ctx->stream);
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    if (r != 0) { cudaFree(d_max); cudaFree(d_bad); return fail(ctx, KM_ERR_NCCL, std::string("ncclAllGather: ") + g_nccl.get_error_string(r)); }
+    if (e == cudaSuccess) {
+      n_total = 0;
+      for (int q = 0; q < ctx->world; q++) {
+        hmax = std::max(hmax, h_out[3 * q]);
+        hbad |= (h_out[3 * q + 1] != 0.0);
+        if (q < ctx->rank) i0 += (int64_t)h_out[3 * q + 2];
+        n_total += (int64_t)h_out[3 * q + 2];
+      }
+    }
+  }
+  cudaFree(d_max);
+  cudaFree(d_bad);
+  KM_CUDA(ctx, e);
+  if (hbad) { free_points(ctx); return fail(ctx, KM_ERR_NONFINITE, "points contain NaN or Inf"); }
+  ctx->maxabs = hmax;
+  ctx->n_total = n_total;
+  ctx->i0 = i0;
+  ctx->have_points = true;
+  km_status s = push_state(ctx);
+  if (s != KM_OK) return s;
+  s = reset_labels(ctx);
+  if (s != KM_OK) return s;
+  if (ctx->have_centroids) {
+    if (ctx->d * (int64_t)ctx->k * 2 + ctx->k + KM_ACC_SCALARS != ctx->acc_len) {
+      free_centroids(ctx);  // shape changed under the old centroids
+    } else {
+      KM_CUDA(ctx, km_launch_prepare_centroids(ctx->c64, ctx->chi, ctx->clo, (int64_t)ctx->k * ctx->d, ctx->state,
+                                               ctx->maxabs, ctx->d, ctx->stream, &ctx->launches));
+    }
+  }
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
+static km_status check_shape(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype) {
+  if (n < 0 || d < 1 || d > KM_MAX_D) return fail(ctx, KM_ERR_INVALID_ARG, "need n >= 0 and 1 <= d <= 65536");
+  if (dtype != KM_DTYPE_F32 && dtype != KM_DTYPE_F64) return fail(ctx, KM_ERR_INVALID_ARG, "dtype must be KM_DTYPE_F32 or KM_DTYPE_F64");
+  return KM_OK;
+}
+
+static km_status alloc_points(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype, bool alloc_x) {
+  free_points(ctx);
+  if (ctx->have_centroids && ctx->d != d) free_centroids(ctx);
+  ctx->n = n; ctx->d = d; ctx->dtype = dtype;
+  size_t bytes = (size_t)n * d * elt_size(dtype);
+  if (alloc_x) {
+    KM_CUDA(ctx, cudaMalloc(&ctx->x, std::max<size_t>(bytes, 16)));
+    ctx->own_x = true;
+  }
+  KM_CUDA(ctx, cudaMalloc(&ctx->labels, std::max<size_t>((size_t)n * sizeof(int32_t), 16)));
+  return KM_OK;
+}
+
+// ------------------------------------------------------------------ life cycle
+extern "C" int32_t km_abi_version(void) { return KM_ABI_VERSION; }
+
+extern "C" const char *km_last_error(const km_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
+  if (!out) return fail(nullptr, KM_ERR_INVALID_ARG, "km_create: out is NULL");
+  *out = nullptr;
+  km_config c;
+  memset(&c, 0, sizeof(c));
+  c.struct_size = sizeof(km_config);
+  c.exact_inertia = 1;
+  if (cfg) {
+    if (cfg->struct_size != (int32_t)sizeof(km_config)) return fail(nullptr, KM_ERR_INVALID_ARG, "km_config.struct_size mismatch");
+    c = *cfg;
+  }
+  if (c.path < KM_PATH_AUTO || c.path > KM_PATH_TENSOR) return fail(nullptr, KM_ERR_INVALID_ARG, "km_config.path out of range");
+  if (c.update_mode != KM_UPDATE_INCREMENTAL && c.update_mode != KM_UPDATE_FULL)
+    return fail(nullptr, KM_ERR_INVALID_ARG, "km_config.update_mode out of range");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, KM_ERR_CUDA, std::string("no usable CUDA device (libkmeans has no CPU fallback): ") +
+                                          (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+  if (c.device < 0 || c.device >= ndev) return fail(nullptr, KM_ERR_INVALID_ARG, "km_config.device out of range");
+  km_ctx *ctx = new km_ctx();
+  ctx->cfg = c;
+  ctx->device = c.device;
+  for (int q = 0; q < KM_RING; q++) ctx->ring_ev[q] = nullptr;
+#define KM_CREATE_CUDA(expr)                                                                  \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      g_create_err = std::string(#expr) + ": " + cudaGetErrorString(_e);                      \
+      km_destroy(ctx);                                                                        \
+      return _e == cudaErrorMemoryAllocation ? KM_ERR_OOM : KM_ERR_CUDA;                      \
+    }                                                                                         \
+  } while (0)
+  KM_CREATE_CUDA(cudaSetDevice(ctx->device));
+  KM_CREATE_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device));
+  KM_CREATE_CUDA(cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+  if (c.stream) {
+    ctx->stream = (cudaStream_t)c.stream;
+  } else {
+    KM_CREATE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    ctx->own_stream = true;
+  }
+  KM_CREATE_CUDA(cudaMalloc(&ctx->state, sizeof(KmState)));
+  KM_CREATE_CUDA(cudaMemset(ctx->state, 0, sizeof(KmState)));
+  KM_CREATE_CUDA(cudaHostAlloc((void **)&ctx->ring, sizeof(KmStatSlot) * KM_RING, cudaHostAllocMapped));
+  memset(ctx->ring, 0, sizeof(KmStatSlot) * KM_RING);
+  KM_CREATE_CUDA(cudaHostGetDevicePointer((void **)&ctx->ring_dev, ctx->ring, 0));
+  for (int q = 0; q < KM_RING; q++) KM_CREATE_CUDA(cudaEventCreateWithFlags(&ctx->ring_ev[q], cudaEventDisableTiming));
+  KM_CREATE_CUDA(cudaEventCreate(&ctx->ev0));
+  KM_CREATE_CUDA(cudaEventCreate(&ctx->ev1));
+#undef KM_CREATE_CUDA
+  *out = ctx;
+  return KM_OK;
+}
+
+extern "C" km_status km_destroy(km_ctx *ctx) {
+  if (!ctx) return KM_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->nccl_comm && g_nccl.comm_destroy) g_nccl.comm_destroy(ctx->nccl_comm);
+  free_points(ctx);
+  free_centroids(ctx);
+  if (ctx->state) cudaFree(ctx->state);
+  if (ctx->ring) cudaFreeHost(ctx->ring);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (int q = 0; q < KM_RING; q++) if (ctx->ring_ev[q]) cudaEventDestroy(ctx->ring_ev[q]);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return KM_OK;
+}
+
+extern "C" km_status km_host_alloc(void **out, uint64_t bytes) {
+  if (!out) return KM_ERR_INVALID_ARG;
+  *out = nullptr;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) return fail(nullptr, e == cudaErrorMemoryAllocation ? KM_ERR_OOM : KM_ERR_CUDA,
+                                    std::string("cudaHostAlloc: ") + cudaGetErrorString(e));
+  return KM_OK;
+}
+extern "C" km_status km_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+  return KM_OK;
+}
+
+// ------------------------------------------------------------------ multi-GPU
+extern "C" km_status km_comm_unique_id(void *out128) {
+  if (!out128) return KM_ERR_INVALID_ARG;
+  std::string why;
+  if (!nccl_load(why)) return fail(nullptr, KM_ERR_NCCL, why);
+  KmNcclUniqueId id;
+  int r = g_nccl.get_unique_id(&id);
+  if (r != 0) return fail(nullptr, KM_ERR_NCCL, std::string("ncclGetUniqueId: ") + g_nccl.get_error_string(r));
+  memcpy(out128, &id, sizeof(id));
+  return KM_OK;
+}
+
+extern "C" km_status km_comm_init(km_ctx *ctx, const void *id128, int32_t rank, int32_t world) {
+  KM_BIND(ctx);
+  if (!id128 || world < 1 || rank < 0 || rank >= world) return fail(ctx, KM_ERR_INVALID_ARG, "km_comm_init: bad rank/world/id");
+  if (ctx->have_points) return fail(ctx, KM_ERR_STATE, "km_comm_init must precede km_upload_points / km_generate_blobs");
+  if (ctx->nccl_comm) return fail(ctx, KM_ERR_STATE, "communicator already initialised");
+  std::string why;
+  if (!nccl_load(why)) return fail(ctx, KM_ERR_NCCL, why);
+  KmNcclUniqueId id;
+  memcpy(&id, id128, sizeof(id));
+  KM_NCCL(ctx, g_nccl.comm_init_rank(&ctx->nccl_comm, world, id, rank));
+  ctx->rank = rank;
+  ctx->world = world;
+  return KM_OK;
+}
+
+// ------------------------------------------------------------------ a1: store
+extern "C" km_status km_upload_points(km_ctx *ctx, const void *host, int64_t n, int32_t d, int32_t dtype) {
+  KM_BIND(ctx);
+  km_status s = check_shape(ctx, n, d, dtype);
+  if (s != KM_OK) return s;
+  if (n > 0 && !host) return fail(ctx, KM_ERR_INVALID_ARG, "km_upload_points: host is NULL");
+  s = alloc_points(ctx, n, d, dtype, true);
+  if (s != KM_OK) return s;
+  s = copy_h2d(ctx, ctx->x, host, (size_t)n * d * elt_size(dtype));
+  if (s != KM_OK) return s;
+  return adopt_points(ctx);
+}
+
+extern "C" km_status km_attach_points(km_ctx *ctx, const void *device, int64_t n, int32_t d, int32_t dtype) {
+  KM_BIND(ctx);
+  km_status s = check_shape(ctx, n, d, dtype);
+  if (s != KM_OK) return s;
+  if (n > 0 && !device) return fail(ctx, KM_ERR_INVALID_ARG, "km_attach_points: device pointer is NULL");
+  if (reinterpret_cast<uintptr_t>(device) & 15) return fail(ctx, KM_ERR_INVALID_ARG, "km_attach_points: pointer must be 16-byte aligned");
+  s = alloc_points(ctx, n, d, dtype, false);
+  if (s != KM_OK) return s;
+  ctx->x = const_cast<void *>(device);
+  ctx->own_x = false;
+  return adopt_points(ctx);
+}
+
+extern "C" km_status km_generate_blobs(km_ctx *ctx, int64_t n, int64_t i0, int32_t d, int32_t k_true, uint64_t seed,
+                                       double sigma) {
+  KM_BIND(ctx);
+  km_status s = check_shape(ctx, n, d, KM_DTYPE_F32);
+  if (s != KM_OK) return s;
+  if (k_true < 1 || i0 < 0) return fail(ctx, KM_ERR_INVALID_ARG, "km_generate_blobs: need k_true >= 1 and i0 >= 0");
+  s = alloc_points(ctx, n, d, KM_DTYPE_F32, true);
+  if (s != KM_OK) return s;
+  KM_CUDA(ctx, km_launch_gen_blobs((float *)ctx->x, n, i0, d, k_true, seed, sigma, ctx->sm_count, ctx->stream, &ctx->launches));
+  s = adopt_points(ctx);
+  if (s != KM_OK) return s;
+  if (ctx->world == 1) ctx->i0 = 0;  // a single rank's rows are the job's rows 0..n-1 whatever slice it generated
+  return KM_OK;
+}
+
+extern "C" km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t n) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
+  if (i0 < 0 || n < 0 || i0 + n > ctx->n || (n > 0 && !host)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_points: range outside the shard");
+  size_t row = (size_t)ctx->d * elt_size(ctx->dtype);
+  return copy_d2h(ctx, host, (const char *)ctx->x + (size_t)i0 * row, (size_t)n * row);
+}
+
+// ------------------------------------------------------------------ a2: initialisation
+static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k) {
+  const int32_t d = ctx->d;
+  const KmAccLayout L = km_acc_layout(k, d);
+  if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len) {
+    free_centroids(ctx);
+    size_t kd = (size_t)k * d;
+    KM_CUDA(ctx, cudaMalloc(&ctx->c64, kd * sizeof(double)));
+    KM_CUDA(ctx, cudaMalloc(&ctx->chi, kd * sizeof(float)));
+    KM_CUDA(ctx, cudaMalloc(&ctx->clo, kd * sizeof(float)));
+    KM_CUDA(ctx, cudaMalloc(&ctx->acc, (size_t)L.len * sizeof(long long)));
+    if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
+    else ctx->acc_global = ctx->acc;
+    ctx->k = k;
+    ctx->acc_len = L.len;
+    ctx->have_centroids = true;
+    km_status s = reset_labels(ctx);  // k changed: old labels mean nothing
+    if (s != KM_OK) return s;
+  }
+  KM_CUDA(ctx, cudaMemcpyAsync(ctx->c64, c_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // c_host is borrowed for this call only
+  KM_CUDA(ctx, km_launch_prepare_centroids(ctx->c64, ctx->chi, ctx->clo, (int64_t)k * d, ctx->state, ctx->maxabs, d,
+                                           ctx->stream, &ctx->launches));
+  return KM_OK;
+}
+
+extern "C" km_status km_set_centroids(km_ctx *ctx, const double *c, int32_t k) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "km_set_centroids: upload or generate points first (d is taken from them)");
+  if (!c || k < 1 || k > KM_MAX_K) return fail(ctx, KM_ERR_INVALID_ARG, "km_set_centroids: need c != NULL and 1 <= k <= 2^20");
+  for (int64_t e = 0; e < (int64_t)k * ctx->d; e++)
+    if (!std::isfinite(c[e])) return fail(ctx, KM_ERR_NONFINITE, "centroids contain NaN or Inf");
+  return install_centroids(ctx, c, k);
+}
+
+// A7: first k picks of a seeded partial Fisher-Yates over the job's indices — the loop of
+// /root/reference/app.mjs:163 cut to k swaps, Math.random() replaced by splitmix64.
+static void forgy_indices(int64_t n, int32_t k, uint64_t seed, std::vector<int64_t> &out) {
+  std::vector<std::pair<int64_t, int64_t>> moved;  // displaced slots only
+  auto get = [&](int64_t key) { for (auto &m : moved) if (m.first == key) return m.second; return key; };
+  auto set = [&](int64_t key, int64_t val) { for (auto &m : moved) if (m.first == key) { m.second = val; return; } moved.emplace_back(key, val); };
+  uint64_t state = seed;
+  out.resize(k);
+  for (int32_t s = 0; s < k; s++) {
+    int64_t i = n - 1 - s;
+    uint64_t r = km_splitmix64(state);
+    state += KM_GAMMA;
+    double u = (double)(r >> 11) * 0x1.0p-53;
+    int64_t j = (int64_t)floor(u * (double)(i + 1));
+    int64_t vi = get(i), vj = get(j);
+    set(i, vj);
+    set(j, vi);
+    out[s] = vj;
+  }
+}
+
+extern "C" km_status km_init_forgy(km_ctx *ctx, int32_t k, uint64_t seed) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "km_init_forgy: no points");
+  if (k < 1 || k > KM_MAX_K || k > ctx->n_total) return fail(ctx, KM_ERR_INVALID_ARG, "km_init_forgy: need 1 <= k <= N");
+  std::vector<int64_t> idx;
+  forgy_indices(ctx->n_total, k, seed, idx);
+  const int32_t d = ctx->d;
+  const size_t row = (size_t)d * elt_size(ctx->dtype);
+  std::vector<double> c((size_t)k * d, 0.0);
+  std::vector<char> tmp(row);
+  for (int32_t s = 0; s < k; s++) {
+    int64_t g = idx[s];
+    if (g < ctx->i0 || g >= ctx->i0 + ctx->n) continue;  // another rank owns this row
+    KM_CUDA(ctx, cudaMemcpyAsync(tmp.data(), (const char *)ctx->x + (size_t)(g - ctx->i0) * row, row, cudaMemcpyDeviceToHost, ctx->stream));
+    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int32_t t = 0; t < d; t++)
+      c[(size_t)s * d + t] = ctx->dtype == KM_DTYPE_F32 ? (double)((const float *)tmp.data())[t] : ((const double *)tmp.data())[t];
+  }
+  if (ctx->world > 1) {
+    // each row is owned by exactly one rank; the others contribute exact zeros
+    double *d_buf = nullptr;
+    KM_CUDA(ctx, cudaMalloc(&d_buf, c.size() * sizeof(double)));
+    cudaError_t e = cudaMemcpyAsync(d_buf, c.data(), c.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+    int r = 0;
+    if (e == cudaSuccess) r = g_nccl.all_reduce(d_buf, d_buf, c.size(), KM_NCCL_FLOAT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream);
+    if (e == cudaSuccess && r == 0) e = cudaMemcpyAsync(c.data(), d_buf, c.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && r == 0) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_buf);
+    if (r != 0) return fail(ctx, KM_ERR_NCCL, std::string("ncclAllReduce: ") + g_nccl.get_error_string(r));
+    KM_CUDA(ctx, e);
+  }
+  return install_centroids(ctx, c.data(), k);
+}
+
+// ------------------------------------------------------------------ a3/a4/a5: the iteration
+static km_status ready(km_ctx *ctx) {
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points: call km_upload_points / km_attach_points / km_generate_blobs");
+  if (!ctx->have_centroids) return fail(ctx, KM_ERR_STATE, "no centroids: call km_set_centroids / km_init_forgy");
+  return KM_OK;
+}
+
+static int pick_path(km_ctx *ctx) {
+  int want = ctx->cfg.path;
+  bool small_ok = km_small_path_supported(ctx->d, ctx->k, ctx->dtype, ctx->max_smem_optin);
+  if (want == KM_PATH_AUTO) return small_ok ? KM_PATH_FILTER_F32 : KM_PATH_DIRECT_F64;
+  return want;
+}
+
+static km_status enqueue_assign(km_ctx *ctx) {
+  KmAssignArgs a;
+  a.x = ctx->x; a.dtype = ctx->dtype; a.n = ctx->n; a.d = ctx->d; a.k = ctx->k;
+  a.labels = ctx->labels; a.c64 = ctx->c64; a.chi = ctx->chi; a.clo = ctx->clo;
+  a.acc = ctx->acc; a.state = ctx->state;
+  a.incremental = ctx->cfg.update_mode == KM_UPDATE_INCREMENTAL;
+  a.exact_inertia = ctx->cfg.exact_inertia;
+  a.sm_count = ctx->sm_count; a.max_smem_optin = ctx->max_smem_optin; a.stream = ctx->stream;
+  const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
+  if (!a.incremental)  // full mode: sums and counts are rebuilt from nothing every pass
+    KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)L.scal * sizeof(long long), ctx->stream));
+  int path = pick_path(ctx);
+  switch (path) {
+    case KM_PATH_DIRECT_F64:
+      KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
+      break;
+    case KM_PATH_FILTER_F32:
+      if (!km_small_path_supported(ctx->d, ctx->k, ctx->dtype, ctx->max_smem_optin))
+        return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8 and k*d*16 bytes of shared memory");
+      KM_CUDA(ctx, km_launch_assign_small(a, &ctx->launches));
+      break;
+    default:
+      return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR is not built yet");
+  }
+  ctx->last_path = path;
+  if (ctx->world > 1)
+    KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
+                                   ctx->nccl_comm, ctx->stream));
+  ctx->labels_fresh = false;
+  return KM_OK;
+}
+
+static km_status enqueue_finalize(km_ctx *ctx, int do_stats, int do_update, int needs_change) {
+  KmStatSlot *slot = nullptr;
+  if (do_stats) {
+    ctx->host_it += 1;
+    slot = ctx->ring_dev + (ctx->host_it % KM_RING);
+  }
+  KM_CUDA(ctx, km_launch_finalize(ctx->acc_global, ctx->acc, ctx->c64, ctx->chi, ctx->clo, ctx->k, ctx->d, ctx->state,
+                                  slot, ctx->maxabs, do_stats, do_update, needs_change, 0, ctx->stream, &ctx->launches));
+  if (do_stats) KM_CUDA(ctx, cudaEventRecord(ctx->ring_ev[ctx->host_it % KM_RING], ctx->stream));
+  return KM_OK;
+}
+
+static void fill_stats(km_ctx *ctx, const KmStatSlot &s, km_stats *out, float ms) {
+  if (!out) return;
+  out->iterations = (int32_t)s.it;
+  out->converged = s.changed == 0;
+  out->changed = s.changed;
+  out->inertia = s.inertia;
+  out->rescored = s.rescored;
+  out->n_total = ctx->n_total;
+  out->device_ms = ms;
+  out->path_used = ctx->last_path;
+}
+
+static km_status wait_slot(km_ctx *ctx, int32_t it, KmStatSlot *out) {
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ring_ev[it % KM_RING]));
+  *out = ctx->ring[it % KM_RING];
+  if (out->it != it) return fail(ctx, KM_ERR_STATE, "stats ring overrun");
+  return KM_OK;
+}
+
+extern "C" km_status km_assign(km_ctx *ctx, km_stats *stats) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  if ((s = enqueue_assign(ctx)) != KM_OK) return s;
+  if ((s = enqueue_finalize(ctx, 1, 0, 0)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  KmStatSlot slot;
+  if ((s = wait_slot(ctx, ctx->host_it, &slot)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+  fill_stats(ctx, slot, stats, ms);
+  return KM_OK;
+}
+
+extern "C" km_status km_update(km_ctx *ctx, km_stats *stats) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  if (ctx->labels_fresh) return fail(ctx, KM_ERR_STATE, "km_update: nothing assigned yet");
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  if ((s = enqueue_finalize(ctx, 0, 1, 0)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  if (stats) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    KmStatSlot slot = ctx->ring[ctx->host_it % KM_RING];
+    fill_stats(ctx, slot, stats, ms);
+  }
+  return KM_OK;
+}
+
+extern "C" km_status km_step_async(km_ctx *ctx) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  if ((s = enqueue_assign(ctx)) != KM_OK) return s;
+  return enqueue_finalize(ctx, 1, 1, 1);
+}
+
+extern "C" km_status km_stats_fetch(km_ctx *ctx, km_stats *stats) {
+  KM_BIND(ctx);
+  if (ctx->host_it == 0) return fail(ctx, KM_ERR_STATE, "km_stats_fetch: no step issued");
+  KmStatSlot slot;
+  km_status s = wait_slot(ctx, ctx->host_it, &slot);
+  if (s != KM_OK) return s;
+  fill_stats(ctx, slot, stats, 0.f);
+  return KM_OK;
+}
+
+extern "C" km_status km_step(km_ctx *ctx, km_stats *stats) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  if ((s = km_step_async(ctx)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  KmStatSlot slot;
+  if ((s = wait_slot(ctx, ctx->host_it, &slot)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+  fill_stats(ctx, slot, stats, ms);
+  return KM_OK;
+}
+
+extern "C" km_status km_reset_labels(km_ctx *ctx) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
+  km_status s = reset_labels(ctx);
+  if (s != KM_OK) return s;
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
+// A5.  The device decides by itself whether an iteration's update happens (changed > 0),
+// so the host may keep KM_RUN_LAG iterations in flight: passes issued after convergence
+// change nothing, and the first slot with changed == 0 is the answer.
+extern "C" km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  if (max_iter < 1) return fail(ctx, KM_ERR_INVALID_ARG, "km_run: max_iter must be >= 1");
+  if ((s = reset_labels(ctx)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  int32_t issued = 0, checked = 0;
+  KmStatSlot last;
+  memset(&last, 0, sizeof(last));
+  bool done = false;
+  while (!done) {
+    while (issued < max_iter && issued - checked < KM_RUN_LAG + 1) {
+      if ((s = enqueue_assign(ctx)) != KM_OK) return s;
+      issued++;
+      // the update after the max_iter-th assign never happens (A5)
+      if ((s = enqueue_finalize(ctx, 1, issued < max_iter, 1)) != KM_OK) return s;
+    }
+    if ((s = wait_slot(ctx, checked + 1, &last)) != KM_OK) return s;
+    checked++;
+    if (last.changed == 0 || checked == max_iter) done = true;
+  }
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));  // drains the speculative passes too
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+  // speculative passes ran past the answer: rewind the iteration counters to it
+  ctx->host_it = checked;
+  KM_CUDA(ctx, cudaMemcpyAsync(&ctx->state->it, &ctx->host_it, sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->ring[checked % KM_RING] = last;
+  fill_stats(ctx, last, stats, ms);
+  return KM_OK;
+}
+
+// ------------------------------------------------------------------ results
+extern "C" km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
+  if (n != ctx->n || (n > 0 && !out)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_labels: n must equal the shard size");
+  return copy_d2h(ctx, out, ctx->labels, (size_t)n * sizeof(int32_t));
+}
+
+extern "C" km_status km_get_centroids(km_ctx *ctx, double *out) {
+  KM_BIND(ctx);
+  if (!ctx->have_centroids || !out) return fail(ctx, KM_ERR_STATE, "no centroids");
+  return copy_d2h(ctx, out, ctx->c64, (size_t)ctx->k * ctx->d * sizeof(double));
+}
+
+static km_status fetch_acc(km_ctx *ctx, std::vector<long long> &h) {
+  if (!ctx->have_centroids) return fail(ctx, KM_ERR_STATE, "no centroids");
+  h.resize((size_t)ctx->acc_len);
+  // in incremental mode the local table is always current; the all-reduced copy is as of
+  // the last assign, which is what "the whole job" means
+  return copy_d2h(ctx, h.data(), ctx->acc_global, h.size() * sizeof(long long));
+}
+
+extern "C" km_status km_get_counts(km_ctx *ctx, int64_t *out) {
+  KM_BIND(ctx);
+  if (!out) return fail(ctx, KM_ERR_INVALID_ARG, "out is NULL");
+  std::vector<long long> h;
+  km_status s = fetch_acc(ctx, h);
+  if (s != KM_OK) return s;
+  const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
+  for (int32_t j = 0; j < ctx->k; j++) out[j] = h[(size_t)L.cnt + j];
+  return KM_OK;
+}
+
+extern "C" km_status km_get_balance(km_ctx *ctx, int64_t *max_out, int64_t *min_out, int64_t *gap_out, double *ratio_out) {
+  KM_BIND(ctx);
+  std::vector<long long> h;
+  km_status s = fetch_acc(ctx, h);
+  if (s != KM_OK) return s;
+  const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
+  long long mx = h[(size_t)L.cnt], mn = h[(size_t)L.cnt];
+  for (int32_t j = 1; j < ctx->k; j++) { mx = std::max(mx, h[(size_t)L.cnt + j]); mn = std::min(mn, h[(size_t)L.cnt + j]); }
+  if (max_out) *max_out = mx;
+  if (min_out) *min_out = mn;
+  if (gap_out) *gap_out = mx - mn;
+  // /root/reference/app.mjs:493 — ratio = min ? max/min : (max ? Infinity : 1)
+  if (ratio_out) *ratio_out = mn ? (double)mx / (double)mn : (mx ? INFINITY : 1.0);
+  return KM_OK;
+}
+
+extern "C" km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t params4[4]) {
+  KM_BIND(ctx);
+  std::vector<long long> h;
+  km_status s = fetch_acc(ctx, h);
+  if (s != KM_OK) return s;
+  const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
+  const size_t kd = (size_t)ctx->k * ctx->d;
+  if (sa) for (size_t e = 0; e < kd; e++) sa[e] = h[(size_t)L.sa + e];
+  if (sb) for (size_t e = 0; e < kd; e++) sb[e] = h[(size_t)L.sb + e];
+  if (params4) { params4[0] = ctx->E; params4[1] = ctx->NB; params4[2] = ctx->QB; params4[3] = ctx->qa; }
+  return KM_OK;
+}
+
+extern "C" km_status km_sync(km_ctx *ctx) {
+  KM_BIND(ctx);
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
+extern "C" int64_t km_launch_count(const km_ctx *ctx) { return ctx ? ctx->launches : 0; }

@@ -1,0 +1,158 @@
+// km_common.cuh — shared device/host definitions for libkmeans.so (sm_100a).
+//
+// Semantics are SURVEY.md Appendix A; the reference (schusto/k-means-demo) has no
+// arithmetic to cite for them.  See DESIGN.md for the data layout.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define KM_MAX_K (1 << 20)
+#define KM_MAX_D (1 << 16)
+
+// ---------------------------------------------------------------------------------
+// Accumulator table `acc` (int64, global memory, one per ctx; a second copy holds the
+// all-reduced table when world > 1).  Integer adds are associative, so any order of
+// atomics, any blocking and any number of GPUs give the same bits.
+//   [0, kd)           Sa   coarse limb of sum_j[t]
+//   [kd, 2kd)         Sb   fine limb
+//   [2kd, 2kd+k)      member counts
+//   [2kd+k + 0]       changed      (per iteration)
+//   [2kd+k + 1]       inertia limb a
+//   [2kd+k + 2]       inertia limb b
+//   [2kd+k + 3]       rescored
+// ---------------------------------------------------------------------------------
+#define KM_ACC_SCALARS 4
+#define KM_ACC_CHANGED 0
+#define KM_ACC_INERTIA_A 1
+#define KM_ACC_INERTIA_B 2
+#define KM_ACC_RESCORED 3
+
+struct KmAccLayout {
+  int64_t sa, sb, cnt, scal, len;
+};
+static inline __host__ __device__ KmAccLayout km_acc_layout(int32_t k, int32_t d) {
+  KmAccLayout L;
+  int64_t kd = (int64_t)k * d;
+  L.sa = 0; L.sb = kd; L.cnt = 2 * kd; L.scal = 2 * kd + k; L.len = 2 * kd + k + KM_ACC_SCALARS;
+  return L;
+}
+
+// Device-resident per-ctx state that one kernel hands to the next without the host.
+struct KmState {
+  double scale_a;        // 2^qa : point value -> coarse limb units
+  double scale_b;        // 2^QB : fraction    -> fine limb units
+  double inertia_scale;  // 2^qi : winner distance -> coarse limb units
+  double cmax;           // max |c_jt| over the current centroids
+  float tau_hilo;        // absolute error term of the hi/lo binary32 filter (small-d path)
+  float tau_hi;          // absolute error term of the hi-only binary32 filter (tiled path)
+  int32_t QB, qa, qi, E;
+  unsigned int ticket;   // last-block election in the finalize kernel
+  int32_t it;            // assign steps since the last label reset
+  unsigned long long cmax_bits;  // scratch for the finalize kernel's max reduction
+};
+
+// One slot of the pinned-host stats ring the finalize kernel writes.
+struct KmStatSlot {
+  long long it;
+  long long changed;
+  double inertia;
+  long long rescored;
+  int updated;   // 1 if this finalize rewrote the centroids
+  int pad;
+};
+
+// ---------------------------------------------------------------------------------
+// A8 generator (libm-free; bit-identical on host and device)
+// ---------------------------------------------------------------------------------
+#define KM_GAMMA 0x9E3779B97F4A7C15ULL
+#define KM_CENTRE_TAG 0xC3A5C85C97CB3127ULL
+
+static inline __host__ __device__ uint64_t km_splitmix64(uint64_t z) {
+  z += KM_GAMMA;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+static inline __host__ __device__ uint64_t km_hash3(uint64_t seed, uint64_t a, uint64_t b) {
+  return km_splitmix64(seed ^ (a * KM_GAMMA) ^ (b * 0xBF58476D1CE4E5B9ULL));
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------------
+// Order-free fixed point: value -> (coarse, fine) int64 limbs.  All operations are exact
+// or a single deterministic rounding of that one value, so the sum of limbs depends on
+// nothing but the multiset of inputs.
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ void km_fixed_split(double v, double scale_a, double scale_b,
+                                               long long &a, long long &b) {
+  double xs = v * scale_a;            // power-of-two scaling: exact
+  double tr = trunc(xs);
+  a = __double2ll_rz(xs);
+  double fr = __dsub_rn(xs, tr);      // exact
+  b = __double2ll_rn(fr * scale_b);   // ties to even
+}
+
+// (Sa * 2^QB + Sb) * 2^-shift, rounded once to binary64 (ties to even).
+__device__ __forceinline__ double km_fixed_to_double(long long Sa, long long Sb, int QB, int shift) {
+  // 128-bit signed T = Sa << QB  +  Sb   (QB in [1, 61])
+  unsigned long long lo = (unsigned long long)Sa << QB;
+  long long hi = Sa >> (64 - QB);
+  unsigned long long lo2 = lo + (unsigned long long)Sb;
+  long long hi2 = hi + (Sb >> 63) + (lo2 < lo ? 1 : 0);
+  if (hi2 == 0 && lo2 == 0) return 0.0;
+  bool neg = hi2 < 0;
+  unsigned long long mh = (unsigned long long)hi2, ml = lo2;
+  if (neg) { ml = ~ml + 1ULL; mh = ~mh + (ml == 0 ? 1ULL : 0ULL); }
+  int hb = mh ? 127 - __clzll((long long)mh) : 63 - __clzll((long long)ml);
+  unsigned long long mant;
+  int e2 = 0;
+  if (hb <= 52) {
+    mant = ml;
+  } else {
+    int sh = hb - 52;  // 1..75
+    // q = m >> sh ; rem = m & (2^sh - 1)
+    unsigned long long q, rem_hi, rem_lo, half_hi, half_lo;
+    if (sh >= 64) {
+      q = mh >> (sh - 64);
+      rem_hi = (sh == 64) ? 0ULL : (mh & ((1ULL << (sh - 64)) - 1ULL));
+      rem_lo = ml;
+      half_hi = (sh == 64) ? 0ULL : (1ULL << (sh - 65));
+      half_lo = (sh == 64) ? (1ULL << 63) : 0ULL;
+    } else {
+      q = (ml >> sh) | (mh << (64 - sh));   // mh << (64-sh) is safe: sh in [1,63]
+      rem_hi = 0ULL;
+      rem_lo = ml & ((1ULL << sh) - 1ULL);
+      half_hi = 0ULL;
+      half_lo = 1ULL << (sh - 1);
+    }
+    mant = q;
+    bool gt = (rem_hi > half_hi) || (rem_hi == half_hi && rem_lo > half_lo);
+    bool eq = (rem_hi == half_hi) && (rem_lo == half_lo);
+    if (gt || (eq && (mant & 1ULL))) mant++;
+    e2 = sh;
+  }
+  double v = scalbn((double)mant, e2 - shift);
+  return neg ? -v : v;
+}
+
+__device__ __forceinline__ void km_atomic_add_ll(long long *p, long long v) {
+  atomicAdd(reinterpret_cast<unsigned long long *>(p), (unsigned long long)v);
+}
+
+// binary64 distance in the oracle's exact operation order (A1): no FMA contraction.
+template <typename XT>
+__device__ __forceinline__ double km_dist2_f64(const XT *__restrict__ xrow, const double *__restrict__ c, int d) {
+  double acc = 0.0;
+  for (int t = 0; t < d; t++) {
+    double df = __dsub_rn((double)xrow[t], c[t]);
+    acc = __dadd_rn(acc, __dmul_rn(df, df));
+  }
+  return acc;
+}
+
+__device__ __forceinline__ long long km_warp_sum_ll(long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+#endif  // __CUDACC__

@@ -1,0 +1,96 @@
+// km_internal.h — host-side context and kernel launcher prototypes (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/kmeans.h"
+#include "km_common.cuh"
+
+#define KM_RING 8      // stats slots in pinned host memory
+#define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
+
+struct km_ctx {
+  km_config cfg;
+  int device = 0;
+  int sm_count = 148;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::string err;
+
+  // ---- a1: store
+  void *x = nullptr;          // device, n x d row-major
+  bool own_x = false;
+  int dtype = KM_DTYPE_F32;
+  int64_t n = 0;              // this rank's shard
+  int64_t i0 = 0;             // global index of row 0 of the shard
+  int64_t n_total = 0;
+  int32_t d = 0;
+  double maxabs = 0.0;        // over the whole job
+  bool have_points = false;
+  int32_t *labels = nullptr;  // device, n
+  void *pinned = nullptr;     // staging for uploads / downloads
+  size_t pinned_bytes = 0;
+
+  // ---- centroids
+  int32_t k = 0;
+  bool have_centroids = false;
+  double *c64 = nullptr;      // device k x d, binary64 master
+  float *chi = nullptr;       // device k x d, fl32(c)
+  float *clo = nullptr;       // device k x d, fl32(c - chi)
+
+  // ---- accumulators / state
+  long long *acc = nullptr;         // device, local table
+  long long *acc_global = nullptr;  // device, all-reduced table (world > 1), else == acc
+  int64_t acc_len = 0;
+  KmState *state = nullptr;         // device
+  KmStatSlot *ring = nullptr;       // pinned host, KM_RING slots (device-mapped)
+  KmStatSlot *ring_dev = nullptr;   // device alias of `ring`
+  cudaEvent_t ring_ev[KM_RING];
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int64_t launches = 0;
+  int32_t host_it = 0;              // assign steps issued since the last label reset
+  int32_t last_path = 0;
+  int32_t QB = 0, qa = 0, E = 0, NB = 0;
+  bool labels_fresh = true;         // labels == -1 everywhere, sums zero
+
+  // ---- multi-GPU
+  int rank = 0, world = 1;
+  void *nccl_comm = nullptr;
+};
+
+struct KmAssignArgs {
+  const void *x;
+  int dtype;
+  int64_t n;
+  int32_t d, k;
+  int32_t *labels;
+  const double *c64;
+  const float *chi;
+  const float *clo;
+  long long *acc;
+  KmState *state;
+  int incremental;     // 1: move only re-labelled points; 0: add every point (acc S zeroed)
+  int exact_inertia;
+  int sm_count;
+  int max_smem_optin;
+  cudaStream_t stream;
+};
+
+// each returns cudaError_t and bumps *launches by the number of kernels enqueued
+cudaError_t km_launch_assign_direct(const KmAssignArgs &a, int64_t *launches);
+cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches);
+bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
+
+cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxabs_out /*device*/,
+                           int *nonfinite_out /*device*/, int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int32_t k_true, uint64_t seed,
+                                double sigma, int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_prepare_centroids(const double *c64, float *chi, float *clo, int64_t kd, KmState *state,
+                                        double maxabs_x, int32_t d, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_finalize(const long long *acc_in, long long *acc_local, double *c64, float *chi, float *clo,
+                               int32_t k, int32_t d, KmState *state, KmStatSlot *slot, double maxabs_x,
+                               int do_stats, int do_update, int update_needs_change, int zero_sums,
+                               cudaStream_t s, int64_t *launches);
