@@ -74,7 +74,7 @@ typedef struct km_config {
   int32_t update_mode; /* KM_UPDATE_* */
   int32_t exact_inertia; /* 1: inertia from binary64 winner distances (<=1e-9 rel);
                             0: from the filter's binary32 distances (<=1e-5 rel) */
-  int32_t reserved0;
+  int32_t profile_kernels; /* 1: bracket each assignment kernel with CUDA events (km_kernel_time) */
   void *stream;        /* cudaStream_t to run on, or NULL for a private stream */
 } km_config;
 
@@ -166,6 +166,9 @@ KM_API km_status km_get_balance(km_ctx *ctx, int64_t *max_out, int64_t *min_out,
 KM_API km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t params4[4]);
 
 KM_API km_status km_sync(km_ctx *ctx);
+/* with km_config.profile_kernels: summed device time of the assignment kernels launched
+ * since the last reset (up to 256 are kept), and how many there were */
+KM_API km_status km_kernel_time(km_ctx *ctx, double *ms_sum, int32_t *launches, int32_t reset);
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 KM_API int64_t km_launch_count(const km_ctx *ctx);
 

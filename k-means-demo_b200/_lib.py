@@ -19,7 +19,7 @@ ABI_VERSION = 1
 
 class Config(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("device", C.c_int32), ("path", C.c_int32),
-                ("update_mode", C.c_int32), ("exact_inertia", C.c_int32), ("reserved0", C.c_int32),
+                ("update_mode", C.c_int32), ("exact_inertia", C.c_int32), ("profile_kernels", C.c_int32),
                 ("stream", C.c_void_p)]
 
 
@@ -62,6 +62,7 @@ PROTOTYPES = {
     "km_get_balance": (_i32, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_dbl)]),
     "km_get_sums": (_i32, [_vp, _vp, _vp, _vp]),
     "km_sync": (_i32, [_vp]),
+    "km_kernel_time": (_i32, [_vp, C.POINTER(_dbl), C.POINTER(_i32), _i32]),
     "km_launch_count": (_i64, [_vp]),
 }
 

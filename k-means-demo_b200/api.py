@@ -34,10 +34,11 @@ class KMeansState:
     """One km_ctx: one GPU's shard of the points, the centroids, labels and sums."""
 
     def __init__(self, device=0, path=L.PATH_AUTO, update_mode=L.UPDATE_INCREMENTAL, exact_inertia=True,
-                 stream=None):
+                 stream=None, profile_kernels=False):
         self._lib = L.load()
         cfg = L.Config(struct_size=C.sizeof(L.Config), device=device, path=path, update_mode=update_mode,
-                       exact_inertia=1 if exact_inertia else 0, reserved0=0, stream=stream)
+                       exact_inertia=1 if exact_inertia else 0,
+                       profile_kernels=1 if profile_kernels else 0, stream=stream)
         h = C.c_void_p()
         st = self._lib.km_create(C.byref(cfg), C.byref(h))
         if st != L.OK:
@@ -190,6 +191,12 @@ class KMeansState:
 
     def sync(self):
         self._check(self._lib.km_sync(self._h))
+
+    def kernel_time(self, reset=True):
+        """(summed ms, count) of the assignment kernels since the last reset (profile_kernels=True)."""
+        ms, n = C.c_double(), C.c_int32()
+        self._check(self._lib.km_kernel_time(self._h, C.byref(ms), C.byref(n), 1 if reset else 0))
+        return ms.value, n.value
 
     def launch_count(self):
         return int(self._lib.km_launch_count(self._h))

@@ -210,10 +210,8 @@ static km_status reset_labels(km_ctx *ctx) {
 
 // after the shard is on the device: scan it, agree on the job-wide scale, reset labels
 static km_status adopt_points(km_ctx *ctx) {
-  double *d_max = nullptr;
-  int *d_bad = nullptr;
-  KM_CUDA(ctx, cudaMalloc(&d_max, sizeof(double)));
-  KM_CUDA(ctx, cudaMalloc(&d_bad, sizeof(int)));
+  double *d_max = ctx->scan_max;
+  int *d_bad = ctx->scan_bad;
   cudaError_t e = km_launch_scan(ctx->x, ctx->dtype, ctx->n * (int64_t)ctx->d, d_max, d_bad, ctx->sm_count, ctx->stream,
                                  &ctx->launches);
   double hmax = 0.0;
@@ -237,7 +235,7 @@ static km_status adopt_points(km_ctx *ctx) {
     if (e == cudaSuccess && r == 0) e = cudaStreamSynchronize(ctx->stream);
     if (d_in) cudaFree(d_in);
     if (d_out) cudaFree(d_out);
-    if (r != 0) { cudaFree(d_max); cudaFree(d_bad); return fail(ctx, KM_ERR_NCCL, std::string("ncclAllGather: ") + g_nccl.get_error_string(r)); }
+    if (r != 0) { return fail(ctx, KM_ERR_NCCL, std::string("ncclAllGather: ") + g_nccl.get_error_string(r)); }
     if (e == cudaSuccess) {
       n_total = 0;
       for (int q = 0; q < ctx->world; q++) {
@@ -248,8 +246,6 @@ static km_status adopt_points(km_ctx *ctx) {
       }
     }
   }
-  cudaFree(d_max);
-  cudaFree(d_bad);
   KM_CUDA(ctx, e);
   if (hbad) { free_points(ctx); return fail(ctx, KM_ERR_NONFINITE, "points contain NaN or Inf"); }
   ctx->maxabs = hmax;
@@ -279,6 +275,12 @@ static km_status check_shape(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype) {
 }
 
 static km_status alloc_points(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype, bool alloc_x) {
+  // same shape as last time and we own the buffer: keep the allocations (an upload per
+  // step must not pay cudaMalloc/cudaFree)
+  if (alloc_x && ctx->own_x && ctx->x && ctx->labels && ctx->n == n && ctx->d == d && ctx->dtype == dtype) {
+    ctx->have_points = false;
+    return KM_OK;
+  }
   free_points(ctx);
   if (ctx->have_centroids && ctx->d != d) free_centroids(ctx);
   ctx->n = n; ctx->d = d; ctx->dtype = dtype;
@@ -320,6 +322,7 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   ctx->cfg = c;
   ctx->device = c.device;
   for (int q = 0; q < KM_RING; q++) ctx->ring_ev[q] = nullptr;
+  for (int q = 0; q < KM_PROF_RING; q++) ctx->prof_ev[q][0] = ctx->prof_ev[q][1] = nullptr;
 #define KM_CREATE_CUDA(expr)                                                                  \
   do {                                                                                        \
     cudaError_t _e = (expr);                                                                  \
@@ -340,6 +343,12 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   }
   KM_CREATE_CUDA(cudaMalloc(&ctx->state, sizeof(KmState)));
   KM_CREATE_CUDA(cudaMemset(ctx->state, 0, sizeof(KmState)));
+  KM_CREATE_CUDA(cudaMalloc(&ctx->scan_max, sizeof(double)));
+  KM_CREATE_CUDA(cudaMalloc(&ctx->scan_bad, sizeof(int)));
+  for (int q = 0; q < KM_PROF_RING; q++) {
+    KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][0]));
+    KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][1]));
+  }
   KM_CREATE_CUDA(cudaHostAlloc((void **)&ctx->ring, sizeof(KmStatSlot) * KM_RING, cudaHostAllocMapped));
   memset(ctx->ring, 0, sizeof(KmStatSlot) * KM_RING);
   KM_CREATE_CUDA(cudaHostGetDevicePointer((void **)&ctx->ring_dev, ctx->ring, 0));
@@ -359,6 +368,10 @@ extern "C" km_status km_destroy(km_ctx *ctx) {
   free_points(ctx);
   free_centroids(ctx);
   if (ctx->state) cudaFree(ctx->state);
+  if (ctx->scan_max) cudaFree(ctx->scan_max);
+  if (ctx->scan_bad) cudaFree(ctx->scan_bad);
+  for (int q = 0; q < KM_PROF_RING; q++)
+    for (int w = 0; w < 2; w++) if (ctx->prof_ev[q][w]) cudaEventDestroy(ctx->prof_ev[q][w]);
   if (ctx->ring) cudaFreeHost(ctx->ring);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (int q = 0; q < KM_RING; q++) if (ctx->ring_ev[q]) cudaEventDestroy(ctx->ring_ev[q]);
@@ -574,6 +587,8 @@ static km_status enqueue_assign(km_ctx *ctx) {
   if (!a.incremental)  // full mode: sums and counts are rebuilt from nothing every pass
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)L.scal * sizeof(long long), ctx->stream));
   int path = pick_path(ctx);
+  const bool prof = ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
+  if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
   switch (path) {
     case KM_PATH_DIRECT_F64:
       KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
@@ -587,6 +602,10 @@ static km_status enqueue_assign(km_ctx *ctx) {
       return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR is not built yet");
   }
   ctx->last_path = path;
+  if (prof) {
+    KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][1], ctx->stream));
+    ctx->prof_n++;
+  }
   if (ctx->world > 1)
     KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
                                    ctx->nccl_comm, ctx->stream));
@@ -806,6 +825,21 @@ extern "C" km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t 
 extern "C" km_status km_sync(km_ctx *ctx) {
   KM_BIND(ctx);
   KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
+extern "C" km_status km_kernel_time(km_ctx *ctx, double *ms_sum, int32_t *launches, int32_t reset) {
+  KM_BIND(ctx);
+  double sum = 0.0;
+  for (int q = 0; q < ctx->prof_n; q++) {
+    KM_CUDA(ctx, cudaEventSynchronize(ctx->prof_ev[q][1]));
+    float ms = 0.f;
+    KM_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_ev[q][0], ctx->prof_ev[q][1]));
+    sum += ms;
+  }
+  if (ms_sum) *ms_sum = sum;
+  if (launches) *launches = ctx->prof_n;
+  if (reset) ctx->prof_n = 0;
   return KM_OK;
 }
 

@@ -9,6 +9,7 @@
 
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
+#define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
 
 struct km_ctx {
   km_config cfg;
@@ -54,6 +55,11 @@ struct km_ctx {
   int32_t last_path = 0;
   int32_t QB = 0, qa = 0, E = 0, NB = 0;
   bool labels_fresh = true;         // labels == -1 everywhere, sums zero
+
+  double *scan_max = nullptr;       // device scratch of the upload scan
+  int *scan_bad = nullptr;
+  cudaEvent_t prof_ev[KM_PROF_RING][2];
+  int prof_n = 0;
 
   // ---- multi-GPU
   int rank = 0, world = 1;

@@ -242,19 +242,24 @@ def test_step_and_async_step_equal_run(km):
     x = oracle.gen_blobs(6, 50000, 2, 8)
     c0 = oracle.forgy_init(x, 8, 6)
     ref = gpu_run(km, x, c0, 12)
+    n_it = ref["iterations"]
     with km.KMeansState() as st:
         st.upload_points(x)
         st.set_centroids(c0)
-        for _ in range(ref["iterations"]):
-            s = st.step()
-        assert s["iterations"] == ref["iterations"] and np.array_equal(st.labels(), ref["labels"])
+        # km_run never updates after its last assign (A5): n_it-1 full steps, then one assign
+        for _ in range(n_it - 1):
+            st.step()
+        s = st.assign()
+        assert s["iterations"] == n_it and np.array_equal(st.labels(), ref["labels"])
         assert np.array_equal(st.centroids(), ref["centroids"]) and s["inertia"] == ref["inertia"]
         st.reset_labels()
         st.set_centroids(c0)
-        for _ in range(ref["iterations"]):
+        for _ in range(n_it - 1):
             st.step_async()
         s = st.stats_fetch()
-        assert s["iterations"] == ref["iterations"] and np.array_equal(st.labels(), ref["labels"])
+        assert s["iterations"] == n_it - 1
+        s = st.assign()
+        assert s["iterations"] == n_it and np.array_equal(st.labels(), ref["labels"])
         assert np.array_equal(st.centroids(), ref["centroids"]) and s["inertia"] == ref["inertia"]
         assert st.launch_count() > 0
 
