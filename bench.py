@@ -209,7 +209,12 @@ def run_ours(args, wl):
 
     n, d, k = wl["n"], wl["d"], wl["k"]
     n_total = n * world
-    stream = torch.cuda.current_stream().cuda_stream
+    # a real (non-default) stream shared by torch's events/flush and the library's kernels:
+    # the legacy default stream's handle is 0, which the C ABI reads as "make your own"
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
     st = km.KMeansState(device=local_rank, stream=stream, profile_kernels=True)
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device=dev)

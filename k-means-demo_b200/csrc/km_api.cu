@@ -208,6 +208,16 @@ static km_status reset_labels(km_ctx *ctx) {
   return KM_OK;
 }
 
+static KmFinalizeArgs make_fin(km_ctx *ctx, KmStatSlot *slot, int do_stats, int do_update, int needs_change) {
+  KmFinalizeArgs f;
+  f.fused = 0;
+  f.acc_in = ctx->acc_global; f.acc_local = ctx->acc;
+  f.c64 = ctx->c64; f.chi = ctx->chi; f.clo = ctx->clo;
+  f.k = ctx->k; f.d = ctx->d; f.st = ctx->state; f.slot = slot; f.maxabs_x = ctx->maxabs;
+  f.do_stats = do_stats; f.do_update = do_update; f.update_needs_change = needs_change;
+  return f;
+}
+
 // after the shard is on the device: scan it, agree on the job-wide scale, reset labels
 static km_status adopt_points(km_ctx *ctx) {
   double *d_max = ctx->scan_max;
@@ -260,8 +270,7 @@ static km_status adopt_points(km_ctx *ctx) {
     if (ctx->d * (int64_t)ctx->k * 2 + ctx->k + KM_ACC_SCALARS != ctx->acc_len) {
       free_centroids(ctx);  // shape changed under the old centroids
     } else {
-      KM_CUDA(ctx, km_launch_prepare_centroids(ctx->c64, ctx->chi, ctx->clo, (int64_t)ctx->k * ctx->d, ctx->state,
-                                               ctx->maxabs, ctx->d, ctx->stream, &ctx->launches));
+      KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 0, 0), ctx->stream, &ctx->launches));
     }
   }
   KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -492,8 +501,9 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
   }
   KM_CUDA(ctx, cudaMemcpyAsync(ctx->c64, c_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // c_host is borrowed for this call only
-  KM_CUDA(ctx, km_launch_prepare_centroids(ctx->c64, ctx->chi, ctx->clo, (int64_t)k * d, ctx->state, ctx->maxabs, d,
-                                           ctx->stream, &ctx->launches));
+  // finalize with nothing to consume: rewrites chi/clo from c64 and refreshes the scales
+  KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 0, 0), ctx->stream, &ctx->launches));
+  ctx->use_hilo = false;
   return KM_OK;
 }
 
@@ -575,7 +585,10 @@ static int pick_path(km_ctx *ctx) {
   return want;
 }
 
-static km_status enqueue_assign(km_ctx *ctx) {
+// One assignment pass plus its finalize.  Single rank + small-d path: the assignment
+// kernel's last block finalizes, so the whole iteration is one launch.  Otherwise the
+// NCCL all-reduce of the packed table sits between two kernels.
+static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int needs_change) {
   KmAssignArgs a;
   a.x = ctx->x; a.dtype = ctx->dtype; a.n = ctx->n; a.d = ctx->d; a.k = ctx->k;
   a.labels = ctx->labels; a.c64 = ctx->c64; a.chi = ctx->chi; a.clo = ctx->clo;
@@ -583,10 +596,21 @@ static km_status enqueue_assign(km_ctx *ctx) {
   a.incremental = ctx->cfg.update_mode == KM_UPDATE_INCREMENTAL;
   a.exact_inertia = ctx->cfg.exact_inertia;
   a.sm_count = ctx->sm_count; a.max_smem_optin = ctx->max_smem_optin; a.stream = ctx->stream;
+  a.hilo = ctx->use_hilo ? 1 : 0;
   const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
   if (!a.incremental)  // full mode: sums and counts are rebuilt from nothing every pass
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)L.scal * sizeof(long long), ctx->stream));
-  int path = pick_path(ctx);
+  const int path = pick_path(ctx);
+  KmStatSlot *slot = nullptr;
+  if (do_stats) {
+    ctx->host_it += 1;
+    slot = ctx->ring_dev + (ctx->host_it % KM_RING);
+  }
+  KmFinalizeArgs fin = make_fin(ctx, slot, do_stats, do_update, needs_change);
+  const bool fuse = ctx->world == 1 && path == KM_PATH_FILTER_F32 && ctx->n > 0 && do_stats &&
+                    (int64_t)ctx->k * ctx->d <= 16384;
+  fin.fused = fuse ? 1 : 0;
+  a.fin = fin;
   const bool prof = ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
   if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
   switch (path) {
@@ -595,7 +619,7 @@ static km_status enqueue_assign(km_ctx *ctx) {
       break;
     case KM_PATH_FILTER_F32:
       if (!km_small_path_supported(ctx->d, ctx->k, ctx->dtype, ctx->max_smem_optin))
-        return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8 and k*d*16 bytes of shared memory");
+        return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096 and room for the centroids in shared memory");
       KM_CUDA(ctx, km_launch_assign_small(a, &ctx->launches));
       break;
     default:
@@ -606,21 +630,14 @@ static km_status enqueue_assign(km_ctx *ctx) {
     KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][1], ctx->stream));
     ctx->prof_n++;
   }
-  if (ctx->world > 1)
-    KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
-                                   ctx->nccl_comm, ctx->stream));
   ctx->labels_fresh = false;
-  return KM_OK;
-}
-
-static km_status enqueue_finalize(km_ctx *ctx, int do_stats, int do_update, int needs_change) {
-  KmStatSlot *slot = nullptr;
-  if (do_stats) {
-    ctx->host_it += 1;
-    slot = ctx->ring_dev + (ctx->host_it % KM_RING);
+  if (!fuse) {
+    if (ctx->world > 1)
+      KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
+                                     ctx->nccl_comm, ctx->stream));
+    fin.fused = 0;
+    KM_CUDA(ctx, km_launch_finalize(fin, ctx->stream, &ctx->launches));
   }
-  KM_CUDA(ctx, km_launch_finalize(ctx->acc_global, ctx->acc, ctx->c64, ctx->chi, ctx->clo, ctx->k, ctx->d, ctx->state,
-                                  slot, ctx->maxabs, do_stats, do_update, needs_change, 0, ctx->stream, &ctx->launches));
   if (do_stats) KM_CUDA(ctx, cudaEventRecord(ctx->ring_ev[ctx->host_it % KM_RING], ctx->stream));
   return KM_OK;
 }
@@ -641,6 +658,9 @@ static km_status wait_slot(km_ctx *ctx, int32_t it, KmStatSlot *out) {
   KM_CUDA(ctx, cudaEventSynchronize(ctx->ring_ev[it % KM_RING]));
   *out = ctx->ring[it % KM_RING];
   if (out->it != it) return fail(ctx, KM_ERR_STATE, "stats ring overrun");
+  // filter escalation: hi-only binary32 centroids carry an absolute error ~ d*u*max|c|^2; when
+  // that sends more than 2% of the job to the binary64 re-score, switch to hi/lo pairs
+  if (!ctx->use_hilo && ctx->n_total > 0 && out->rescored * 50 > ctx->n_total) ctx->use_hilo = true;
   return KM_OK;
 }
 
@@ -649,8 +669,7 @@ extern "C" km_status km_assign(km_ctx *ctx, km_stats *stats) {
   km_status s = ready(ctx);
   if (s != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  if ((s = enqueue_assign(ctx)) != KM_OK) return s;
-  if ((s = enqueue_finalize(ctx, 1, 0, 0)) != KM_OK) return s;
+  if ((s = enqueue_pass(ctx, 1, 0, 0)) != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KmStatSlot slot;
   if ((s = wait_slot(ctx, ctx->host_it, &slot)) != KM_OK) return s;
@@ -667,7 +686,7 @@ extern "C" km_status km_update(km_ctx *ctx, km_stats *stats) {
   if (s != KM_OK) return s;
   if (ctx->labels_fresh) return fail(ctx, KM_ERR_STATE, "km_update: nothing assigned yet");
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  if ((s = enqueue_finalize(ctx, 0, 1, 0)) != KM_OK) return s;
+  KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 1, 0), ctx->stream, &ctx->launches));
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
   if (stats) {
@@ -683,8 +702,7 @@ extern "C" km_status km_step_async(km_ctx *ctx) {
   KM_BIND(ctx);
   km_status s = ready(ctx);
   if (s != KM_OK) return s;
-  if ((s = enqueue_assign(ctx)) != KM_OK) return s;
-  return enqueue_finalize(ctx, 1, 1, 1);
+  return enqueue_pass(ctx, 1, 1, 1);
 }
 
 extern "C" km_status km_stats_fetch(km_ctx *ctx, km_stats *stats) {
@@ -738,10 +756,9 @@ extern "C" km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats) {
   bool done = false;
   while (!done) {
     while (issued < max_iter && issued - checked < KM_RUN_LAG + 1) {
-      if ((s = enqueue_assign(ctx)) != KM_OK) return s;
       issued++;
       // the update after the max_iter-th assign never happens (A5)
-      if ((s = enqueue_finalize(ctx, 1, issued < max_iter, 1)) != KM_OK) return s;
+      if ((s = enqueue_pass(ctx, 1, issued < max_iter, 1)) != KM_OK) return s;
     }
     if ((s = wait_slot(ctx, checked + 1, &last)) != KM_OK) return s;
     checked++;

@@ -1,195 +1,340 @@
 // km_assign_small.cu — KM_PATH_FILTER_F32 for small d (1..8): the bandwidth-bound path
 // (BASELINE.json configs[1] and [4]: d=2, k=8 / k=64).
 //
-// One thread per point (vectorised so each lane moves 16 bytes when d is 1, 2 or 4),
-// centroids staged once per block in shared memory as binary32 hi/lo pairs plus the
-// binary64 masters.  Every distance is first taken in binary32; the point is re-scored in
-// binary64 (the oracle's exact operation order) only when the gap between its two best
-// binary32 distances is inside the rigorous error bound of DESIGN.md §5.  Labels are
-// therefore the oracle's, bit for bit, at binary32 cost.  The label compare, the move of
-// re-labelled points between the order-free per-cluster sums, the change count and the
-// inertia are fused into the same pass: x is read exactly once per iteration.
+// Shape of the kernel:
+//   * persistent grid: (SMs x resident blocks) fat blocks stride over tiles of points, so the
+//     per-block prologue (centroids -> shared memory) and epilogue (table flush, scalar
+//     reduction, optional fused finalize) are paid once per SM, not once per tile;
+//   * each lane moves 16 bytes per load when d is 1, 2 or 4 (float4), labels as int2/int4;
+//   * distances in binary32 two dimensions at a time with packed f32x2 add/mul/fma (sm_100a
+//     add.rn.f32x2 / fma.rn.f32x2): a point's (x0,x1) arrives from the vector load already
+//     as an aligned register pair, centroids are stored pre-negated so a centroid is one
+//     broadcast LDS and (x - c) is one packed add;
+//   * top-2 per point on integer keys: (distance bits & ~mask) | centroid index, three
+//     integer min/max per (point, centroid), no selects;
+//   * a point is re-scored in binary64 (the oracle's exact operation order) only when the gap
+//     between its two best keys is inside the rigorous error bound of DESIGN.md §5, so the
+//     labels are the oracle's bit for bit at binary32 cost;
+//   * label compare, move of re-labelled points between the order-free per-cluster sums,
+//     change count and inertia are fused into the same pass: x is read once per iteration;
+//   * optionally the last block to finish also performs the centroid update (finalize), so
+//     a Lloyd iteration is ONE kernel launch.
+#include <cuda_fp16.h>
+
 #include "km_commit.cuh"
+#include "km_finalize.cuh"
 #include "km_internal.h"
 
-#define KM_SMALL_THREADS 256
+#define KM_SMALL_THREADS 512
+
+// Packed binary32 pairs held as one 64-bit register each, so the register allocator keeps
+// a pair together across the centroid loop instead of re-packing it at every use.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
 
 template <int D>
 struct KmSmallCfg {
-  static constexpr int PPT = (D == 1) ? 4 : (D == 2) ? 2 : 1;  // points per thread per tile
+  static constexpr int PPV = (D == 1) ? 4 : (D == 2) ? 2 : 1;   // points per 16-byte vector (else 1 row per "vector")
+  static constexpr int NV = (D <= 4) ? 2 : 1;                   // vectors / rows per thread per tile
+  static constexpr int PPT = PPV * NV;                          // points per thread per tile
+  static constexpr int NP = D / 2;                              // packed dimension pairs per point
+  static constexpr bool TAIL = (D & 1) != 0;                    // odd last dimension handled as a scalar
 };
 
-template <int D>
-__global__ void __launch_bounds__(KM_SMALL_THREADS)
-km_assign_small_kernel(const float *__restrict__ x, int64_t n, int32_t k, int32_t *__restrict__ labels,
-                       const double *__restrict__ c64, const float *__restrict__ chi, const float *__restrict__ clo,
-                       long long *__restrict__ acc, const KmState *__restrict__ st, int incremental,
-                       int exact_inertia, int tab_in_smem) {
-  constexpr int PPT = KmSmallCfg<D>::PPT;
+struct KmSmallParams {
+  const float *x;
+  int64_t n;
+  int32_t k;
+  int32_t *labels;
+  const double *c64;
+  const float *chi;
+  const float *clo;
+  long long *acc;
+  KmState *st;
+  int incremental;
+  int exact_inertia;
+  int tab_in_smem;
+  unsigned key_mask;   // low bits of the distance key that hold the centroid index
+  float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
+  KmFinalizeArgs fin;  // used when fin.fused != 0
+};
+
+template <int D, bool HILO>
+__global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
+  using Cfg = KmSmallCfg<D>;
+  constexpr int PPV = Cfg::PPV, NV = Cfg::NV, PPT = Cfg::PPT, NP = Cfg::NP;
+  constexpr bool TAIL = Cfg::TAIL;
+  constexpr int CW = HILO ? 2 : 1;   // binary32 words per centroid coordinate (hi [, lo])
+  constexpr int CROW = D * CW;       // floats per centroid row: -hi[0..D) then -lo[0..D)
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float *cf = reinterpret_cast<float *>(smem_raw);                    // [k][2D]: hi[D], lo[D]
-  double *cd = reinterpret_cast<double *>(cf + (size_t)k * 2 * D);    // [k][D]
-  long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);
+  const int k = p.k;
+  float *ncf = reinterpret_cast<float *>(smem_raw);                                  // [k][CROW], negated
+  double *cd = reinterpret_cast<double *>(ncf + (((size_t)k * CROW + 3) & ~(size_t)3));  // [k][D] binary64 masters
+  long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);               // optional per-block table
   const KmAccLayout L = km_acc_layout(k, D);
 
   for (int e = threadIdx.x; e < k * D; e += KM_SMALL_THREADS) {
-    const int j = e / D, t = e - j * D;
-    cf[j * 2 * D + t] = chi[e];
-    cf[j * 2 * D + D + t] = clo[e];
-    cd[e] = c64[e];
+    const int jj = e / D, t = e - jj * D;
+    ncf[jj * CROW + t] = -p.chi[e];
+    if (HILO) ncf[jj * CROW + D + t] = -p.clo[e];
+    cd[e] = p.c64[e];
   }
   KmBlockTab T;
   T.L = L;
-  T.tab = tab_in_smem ? stab : acc;
-  if (tab_in_smem) km_tab_zero(stab, L.scal);
+  T.tab = p.tab_in_smem ? stab : p.acc;
+  if (p.tab_in_smem) km_tab_zero(stab, L.scal);
   __syncthreads();
 
-  const double scale_a = st->scale_a, scale_b = st->scale_b, inertia_scale = st->inertia_scale;
-  const float tau2 = st->tau_hilo;                              // already carries the 2.5x margin
-  constexpr float rho2 = 2.5f * (float)(D + 6) * 0x1.0p-24f;
-  KmThreadScalars S;
+  const double scale_a = p.st->scale_a, scale_b = p.st->scale_b, inertia_scale = p.st->inertia_scale;
+  const float tau2 = HILO ? p.st->tau_hilo : p.st->tau_hi;   // absolute part (2.5x margin included)
+  const float rho2 = p.rho2;
+  const unsigned mask = p.key_mask;
+  int changed = 0, rescored = 0;
+  double inertia = 0.0;
 
   const int64_t per_tile = (int64_t)KM_SMALL_THREADS * PPT;
-  const int64_t ntiles = (n + per_tile - 1) / per_tile;
+  const int64_t ntiles = (p.n + per_tile - 1) / per_tile;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t base = (tile * KM_SMALL_THREADS + threadIdx.x) * PPT;
-    float xv[PPT][D];
+    const int64_t tile0 = tile * per_tile;
+    f32x2 xq[PPT][NP > 0 ? NP : 1];  // packed (x[2m], x[2m+1]) pairs, as loaded
+    float xs[PPT];                   // D == 1: the point; odd D: the last coordinate
     int old[PPT];
-    bool live[PPT];
-    if (base + PPT <= n) {
-      // full group: 16-byte loads where the shape allows
-      if constexpr (D == 1 || D == 2 || D == 4) {
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(x + base * D));
-        const float f[4] = {v.x, v.y, v.z, v.w};
+    int64_t pidx[NV];                // first point of each vector / row
+    const bool full = tile0 + per_tile <= p.n;
 #pragma unroll
-        for (int p = 0; p < PPT; p++)
+    for (int v = 0; v < NV; v++) {
+      pidx[v] = tile0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
+      if (full) {
+        const float *row = p.x + pidx[v] * D;
+        if constexpr (D == 1) {
+          const float4 q = __ldg(reinterpret_cast<const float4 *>(row));
+          xs[v * 4 + 0] = q.x; xs[v * 4 + 1] = q.y; xs[v * 4 + 2] = q.z; xs[v * 4 + 3] = q.w;
+          const int4 o = *reinterpret_cast<const int4 *>(p.labels + pidx[v]);
+          old[v * 4 + 0] = o.x; old[v * 4 + 1] = o.y; old[v * 4 + 2] = o.z; old[v * 4 + 3] = o.w;
+        } else if constexpr (D == 2) {
+          const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row));
+          xq[v * 2 + 0][0] = q.x; xq[v * 2 + 1][0] = q.y;
+          const int2 o = *reinterpret_cast<const int2 *>(p.labels + pidx[v]);
+          old[v * 2 + 0] = o.x; old[v * 2 + 1] = o.y;
+        } else {
+          if constexpr (D % 4 == 0) {
 #pragma unroll
-          for (int t = 0; t < D; t++) xv[p][t] = f[p * D + t];
+            for (int m = 0; m < D / 4; m++) {
+              const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row) + m);
+              xq[v][2 * m] = q.x; xq[v][2 * m + 1] = q.y;
+            }
+          } else if constexpr (D % 2 == 0) {
+#pragma unroll
+            for (int m = 0; m < NP; m++) xq[v][m] = __ldg(reinterpret_cast<const unsigned long long *>(row) + m);
+          } else {
+#pragma unroll
+            for (int m = 0; m < NP; m++) xq[v][m] = pk2(__ldg(row + 2 * m), __ldg(row + 2 * m + 1));
+            xs[v] = __ldg(row + D - 1);
+          }
+          old[v] = p.labels[pidx[v]];
+        }
       } else {
 #pragma unroll
-        for (int t = 0; t < D; t++) xv[0][t] = __ldg(x + base * D + t);
-      }
-      if constexpr (PPT == 4) {
-        const int4 o = *reinterpret_cast<const int4 *>(labels + base);
-        old[0] = o.x; old[1] = o.y; old[2] = o.z; old[3] = o.w;
-      } else if constexpr (PPT == 2) {
-        const int2 o = *reinterpret_cast<const int2 *>(labels + base);
-        old[0] = o.x; old[1] = o.y;
-      } else {
-        old[0] = labels[base];
-      }
+        for (int u = 0; u < PPV; u++) {
+          const int64_t i = pidx[v] + u;
+          const bool live = i < p.n;
+          const int q = v * PPV + u;
+          old[q] = live ? p.labels[i] : 0;
 #pragma unroll
-      for (int p = 0; p < PPT; p++) live[p] = true;
-    } else {
-#pragma unroll
-      for (int p = 0; p < PPT; p++) {
-        live[p] = base + p < n;
-        old[p] = live[p] ? labels[base + p] : 0;
-#pragma unroll
-        for (int t = 0; t < D; t++) xv[p][t] = live[p] ? x[(base + p) * D + t] : 0.0f;
+          for (int m = 0; m < NP; m++)
+            xq[q][m] = live ? pk2(p.x[i * D + 2 * m], p.x[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
+          if (D == 1 || TAIL) xs[q] = live ? p.x[i * D + D - 1] : 0.f;
+        }
       }
     }
 
-    float b1[PPT], b2[PPT];
-    int i1[PPT];
+    // ---- binary32 filter, top-2 on integer keys
+    unsigned m1[PPT], m2[PPT];
 #pragma unroll
-    for (int p = 0; p < PPT; p++) { b1[p] = __int_as_float(0x7f800000); b2[p] = b1[p]; i1[p] = 0; }
+    for (int q = 0; q < PPT; q++) { m1[q] = 0xFFFFFFFFu; m2[q] = 0xFFFFFFFFu; }
 
 #pragma unroll 4
     for (int j = 0; j < k; j++) {
-      float hi[D], lo[D];
-      if constexpr (D == 2) {
-        const float4 c = *reinterpret_cast<const float4 *>(cf + j * 4);
-        hi[0] = c.x; hi[1] = c.y; lo[0] = c.z; lo[1] = c.w;
-      } else if constexpr (D == 4) {
-        const float4 h = *reinterpret_cast<const float4 *>(cf + j * 8);
-        const float4 l = *reinterpret_cast<const float4 *>(cf + j * 8 + 4);
-        hi[0] = h.x; hi[1] = h.y; hi[2] = h.z; hi[3] = h.w;
-        lo[0] = l.x; lo[1] = l.y; lo[2] = l.z; lo[3] = l.w;
+      const float *crow = ncf + j * CROW;
+      f32x2 nh[NP > 0 ? NP : 1], nl[NP > 0 ? NP : 1];
+      float th = 0.f, tl = 0.f;
+      if constexpr (D == 2 && !HILO) {
+        nh[0] = *reinterpret_cast<const f32x2 *>(crow);
+      } else if constexpr (D == 2 && HILO) {
+        const ulonglong2 c = *reinterpret_cast<const ulonglong2 *>(crow);
+        nh[0] = c.x; nl[0] = c.y;
       } else {
 #pragma unroll
-        for (int t = 0; t < D; t++) { hi[t] = cf[j * 2 * D + t]; lo[t] = cf[j * 2 * D + D + t]; }
+        for (int m = 0; m < NP; m++) {
+          nh[m] = pk2(crow[2 * m], crow[2 * m + 1]);
+          if (HILO) nl[m] = pk2(crow[D + 2 * m], crow[D + 2 * m + 1]);
+        }
+        if (D == 1 || TAIL) { th = crow[D - 1]; if (HILO) tl = crow[2 * D - 1]; }
       }
 #pragma unroll
-      for (int p = 0; p < PPT; p++) {
-        float dj = 0.0f;
+      for (int q = 0; q < PPT; q++) {
+        float dist;
+        if constexpr (NP > 0) {
+          f32x2 acc2;
 #pragma unroll
-        for (int t = 0; t < D; t++) {
-          const float a = __fsub_rn(xv[p][t], hi[t]);
-          const float b = __fsub_rn(a, lo[t]);
-          dj = fmaf(b, b, dj);
+          for (int m = 0; m < NP; m++) {
+            f32x2 df = add2(xq[q][m], nh[m]);
+            if (HILO) df = add2(df, nl[m]);
+            acc2 = (m == 0) ? mul2(df, df) : fma2(df, df, acc2);
+          }
+          float lo, hi;
+          unpk2(acc2, lo, hi);
+          dist = lo + hi;
+          if constexpr (TAIL) {
+            float dt = xs[q] + th;
+            if (HILO) dt += tl;
+            dist = fmaf(dt, dt, dist);
+          }
+        } else {
+          float dt = xs[q] + th;
+          if (HILO) dt += tl;
+          dist = dt * dt;
         }
-        const bool lt = dj < b1[p];
-        b2[p] = lt ? b1[p] : fminf(b2[p], dj);
-        i1[p] = lt ? j : i1[p];
-        b1[p] = lt ? dj : b1[p];
+        const unsigned key = (__float_as_uint(dist) & ~mask) | (unsigned)j;
+        m2[q] = min(m2[q], max(m1[q], key));
+        m1[q] = min(m1[q], key);
       }
     }
 
+    // ---- per point: ambiguity test, rare binary64 re-score, inertia, commit
     int newlab[PPT];
-    bool any_change = false;
 #pragma unroll
-    for (int p = 0; p < PPT; p++) {
-      newlab[p] = old[p];
-      if (!live[p]) continue;
-      int lab = i1[p];
+    for (int q = 0; q < PPT; q++) {
+      const int64_t i = pidx[q / PPV] + (q % PPV);
+      newlab[q] = old[q];
+      if (!full && i >= p.n) continue;
+      int lab = (int)(m1[q] & mask);
+      float xr[D];
+#pragma unroll
+      for (int m = 0; m < NP; m++) unpk2(xq[q][m], xr[2 * m], xr[2 * m + 1]);
+      if (D == 1 || TAIL) xr[D - 1] = xs[q];
+      const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
+      // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score
+      const bool clear = (b2 - b1) > fmaf(rho2, b2, tau2);
       double best;
-      // unambiguous iff the gap clears the error bound; written so NaN/Inf fall to the re-score
-      const bool clear = (b2[p] - b1[p]) > (rho2 * b2[p] + tau2);
       if (!clear) {
-        S.rescored++;
+        rescored++;
         best = __longlong_as_double(0x7FF0000000000000LL);
         lab = 0;
         for (int j = 0; j < k; j++) {
-          const double dj = km_dist2_f64(xv[p], cd + (size_t)j * D, D);
+          const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
           if (dj < best) { best = dj; lab = j; }
         }
       } else {
-        best = exact_inertia ? km_dist2_f64(xv[p], cd + (size_t)lab * D, D) : (double)b1[p];
+        best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
       }
-      newlab[p] = lab;
-      any_change |= (lab != old[p]);
-      km_commit_point(T, S, xv[p], D, old[p], lab, best, incremental, scale_a, scale_b, inertia_scale);
+      inertia += best;
+      newlab[q] = lab;
+      if (lab != old[q]) {
+        changed++;
+        if (p.incremental) km_move_point(T, xr, D, lab, old[q], scale_a, scale_b);
+      }
+      if (!p.incremental) km_move_point(T, xr, D, lab, -1, scale_a, scale_b);
     }
-    if (any_change) {
-      if (base + PPT <= n) {
-        if constexpr (PPT == 4) {
-          *reinterpret_cast<int4 *>(labels + base) = make_int4(newlab[0], newlab[1], newlab[2], newlab[3]);
-        } else if constexpr (PPT == 2) {
-          *reinterpret_cast<int2 *>(labels + base) = make_int2(newlab[0], newlab[1]);
+#pragma unroll
+    for (int v = 0; v < NV; v++) {
+      bool any = false;
+#pragma unroll
+      for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != old[v * PPV + u];
+      if (!any) continue;
+      if (full) {
+        if constexpr (PPV == 4) {
+          *reinterpret_cast<int4 *>(p.labels + pidx[v]) =
+              make_int4(newlab[v * 4], newlab[v * 4 + 1], newlab[v * 4 + 2], newlab[v * 4 + 3]);
+        } else if constexpr (PPV == 2) {
+          *reinterpret_cast<int2 *>(p.labels + pidx[v]) = make_int2(newlab[v * 2], newlab[v * 2 + 1]);
         } else {
-          labels[base] = newlab[0];
+          p.labels[pidx[v]] = newlab[v];
         }
       } else {
 #pragma unroll
-        for (int p = 0; p < PPT; p++)
-          if (live[p]) labels[base + p] = newlab[p];
+        for (int u = 0; u < PPV; u++)
+          if (pidx[v] + u < p.n) p.labels[pidx[v] + u] = newlab[v * PPV + u];
       }
     }
   }
+
+  // ---- block epilogue: the per-thread inertia partial is made order-free here (one split
+  // per thread), everything beyond this point is integer adds
+  KmThreadScalars S;
+  S.changed = changed;
+  S.rescored = rescored;
+  km_fixed_split(inertia, inertia_scale, scale_b, S.ia, S.ib);
   __syncthreads();
-  if (tab_in_smem) km_tab_flush(stab, acc, L.scal);
-  km_flush_scalars(S, acc, L);
+  if (p.tab_in_smem) km_tab_flush(stab, p.acc, L.scal);
+  km_flush_scalars(S, p.acc, L);
+  if (p.fin.fused) {
+    __shared__ int is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(&p.st->ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (is_last) {
+      __threadfence();
+      if (threadIdx.x == 0) p.st->ticket = 0;
+      km_finalize_block(p.fin);
+    }
+  }
 }
 
-static size_t small_centroid_smem(int32_t d, int32_t k) { return (size_t)k * d * (2 * sizeof(float) + sizeof(double)); }
+static size_t small_centroid_smem(int32_t d, int32_t k, bool hilo) {
+  size_t floats = ((size_t)k * d * (hilo ? 2 : 1) + 3) & ~(size_t)3;
+  return floats * sizeof(float) + (size_t)k * d * sizeof(double);
+}
 
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin) {
-  if (dtype != KM_DTYPE_F32 || d < 1 || d > 8) return false;
-  return small_centroid_smem(d, k) + 4096 <= (size_t)max_smem_optin;
+  if (dtype != KM_DTYPE_F32 || d < 1 || d > 8 || k > 4096) return false;
+  return small_centroid_smem(d, k, true) + 4096 <= (size_t)max_smem_optin / 2;
 }
 
-template <int D>
+template <int D, bool HILO>
 static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   const KmAccLayout L = km_acc_layout(a.k, D);
-  size_t smem = small_centroid_smem(D, a.k);
-  int tab_in_smem = 0;
+  size_t smem = small_centroid_smem(D, a.k, HILO);
+  KmSmallParams p;
+  p.x = (const float *)a.x; p.n = a.n; p.k = a.k; p.labels = a.labels;
+  p.c64 = a.c64; p.chi = a.chi; p.clo = a.clo; p.acc = a.acc; p.st = a.state;
+  p.incremental = a.incremental; p.exact_inertia = a.exact_inertia;
+  p.tab_in_smem = 0;
   const size_t tab_bytes = (size_t)L.scal * sizeof(long long);
-  if (tab_bytes <= 64 * 1024 && smem + tab_bytes + 4096 <= (size_t)a.max_smem_optin) {
-    tab_in_smem = 1;
+  if (tab_bytes <= 48 * 1024 && smem + tab_bytes + 4096 <= (size_t)a.max_smem_optin / 2) {
+    p.tab_in_smem = 1;
     smem += tab_bytes;
   }
-  auto kern = km_assign_small_kernel<D>;
+  int bits = 0;
+  while ((1 << bits) < a.k) bits++;
+  p.key_mask = (1u << bits) - 1u;
+  // (D+6) u for the arithmetic, 2^-(23-bits) for the key truncation, x2.5 margin
+  p.rho2 = 2.5f * ((float)(D + 6) * 0x1.0p-24f + ldexpf(1.0f, bits - 23));
+  p.fin = a.fin;
+  auto kern = km_assign_small_kernel<D, HILO>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -198,27 +343,31 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   if (per_sm < 1) per_sm = 1;
   const int64_t per_tile = (int64_t)KM_SMALL_THREADS * KmSmallCfg<D>::PPT;
   const int64_t ntiles = (a.n + per_tile - 1) / per_tile;
-  const int64_t cap = (int64_t)a.sm_count * per_sm;   // one resident wave, grid-stride over tiles
+  const int64_t cap = (int64_t)a.sm_count * per_sm;   // one resident wave; blocks stride over tiles
   const int grid = (int)(ntiles < cap ? ntiles : cap);
-  kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>((const float *)a.x, a.n, a.k, a.labels, a.c64, a.chi, a.clo, a.acc,
-                                                   a.state, a.incremental, a.exact_inertia, tab_in_smem);
+  kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
   (*launches)++;
   return cudaGetLastError();
 }
 
-cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches) {
-  if (a.n == 0) return cudaSuccess;
-  if ((reinterpret_cast<uintptr_t>(a.x) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15))
-    return cudaErrorMisalignedAddress;
+template <bool HILO>
+static cudaError_t dispatch_small(const KmAssignArgs &a, int64_t *launches) {
   switch (a.d) {
-    case 1: return launch_small<1>(a, launches);
-    case 2: return launch_small<2>(a, launches);
-    case 3: return launch_small<3>(a, launches);
-    case 4: return launch_small<4>(a, launches);
-    case 5: return launch_small<5>(a, launches);
-    case 6: return launch_small<6>(a, launches);
-    case 7: return launch_small<7>(a, launches);
-    case 8: return launch_small<8>(a, launches);
+    case 1: return launch_small<1, HILO>(a, launches);
+    case 2: return launch_small<2, HILO>(a, launches);
+    case 3: return launch_small<3, HILO>(a, launches);
+    case 4: return launch_small<4, HILO>(a, launches);
+    case 5: return launch_small<5, HILO>(a, launches);
+    case 6: return launch_small<6, HILO>(a, launches);
+    case 7: return launch_small<7, HILO>(a, launches);
+    case 8: return launch_small<8, HILO>(a, launches);
     default: return cudaErrorInvalidValue;
   }
+}
+
+cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches) {
+  if (a.n == 0 && !a.fin.fused) return cudaSuccess;
+  if ((reinterpret_cast<uintptr_t>(a.x) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15))
+    return cudaErrorMisalignedAddress;
+  return a.hilo ? dispatch_small<true>(a, launches) : dispatch_small<false>(a, launches);
 }

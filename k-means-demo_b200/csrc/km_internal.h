@@ -6,6 +6,7 @@
 
 #include "../../include/kmeans.h"
 #include "km_common.cuh"
+#include "km_finalize.cuh"
 
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
@@ -54,6 +55,7 @@ struct km_ctx {
   int32_t host_it = 0;              // assign steps issued since the last label reset
   int32_t last_path = 0;
   int32_t QB = 0, qa = 0, E = 0, NB = 0;
+  bool use_hilo = false;            // small-d filter escalated to hi/lo centroid pairs
   bool labels_fresh = true;         // labels == -1 everywhere, sums zero
 
   double *scan_max = nullptr;       // device scratch of the upload scan
@@ -81,6 +83,8 @@ struct KmAssignArgs {
   int exact_inertia;
   int sm_count;
   int max_smem_optin;
+  int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
+  KmFinalizeArgs fin;  // fin.fused = 1: the assignment kernel's last block also finalizes
   cudaStream_t stream;
 };
 
@@ -94,9 +98,4 @@ cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxa
 cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int32_t k_true, uint64_t seed,
                                 double sigma, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, cudaStream_t s, int64_t *launches);
-cudaError_t km_launch_prepare_centroids(const double *c64, float *chi, float *clo, int64_t kd, KmState *state,
-                                        double maxabs_x, int32_t d, cudaStream_t s, int64_t *launches);
-cudaError_t km_launch_finalize(const long long *acc_in, long long *acc_local, double *c64, float *chi, float *clo,
-                               int32_t k, int32_t d, KmState *state, KmStatSlot *slot, double maxabs_x,
-                               int do_stats, int do_update, int update_needs_change, int zero_sums,
-                               cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t *launches);
