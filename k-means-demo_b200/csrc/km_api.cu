@@ -597,6 +597,8 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
   a.exact_inertia = ctx->cfg.exact_inertia;
   a.sm_count = ctx->sm_count; a.max_smem_optin = ctx->max_smem_optin; a.stream = ctx->stream;
   a.hilo = ctx->use_hilo ? 1 : 0;
+  a.scale_a = ldexp(1.0, ctx->qa);
+  a.scale_b = ldexp(1.0, ctx->QB);
   const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
   if (!a.incremental)  // full mode: sums and counts are rebuilt from nothing every pass
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)L.scal * sizeof(long long), ctx->stream));

@@ -57,7 +57,7 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
 template <int D>
 struct KmSmallCfg {
   static constexpr int PPV = (D == 1) ? 4 : (D == 2) ? 2 : 1;   // points per 16-byte vector (else 1 row per "vector")
-  static constexpr int NV = (D <= 4) ? 2 : 1;                   // vectors / rows per thread per tile
+  static constexpr int NV = (D == 1) ? 1 : (D <= 4) ? 2 : 1;    // vectors / rows per thread per round
   static constexpr int PPT = PPV * NV;                          // points per thread per tile
   static constexpr int NP = D / 2;                              // packed dimension pairs per point
   static constexpr bool TAIL = (D & 1) != 0;                    // odd last dimension handled as a scalar
@@ -78,8 +78,77 @@ struct KmSmallParams {
   int tab_in_smem;
   unsigned key_mask;   // low bits of the distance key that hold the centroid index
   float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
+  double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
+  int64_t chunk;       // points per block (multiple of 4)
   KmFinalizeArgs fin;  // used when fin.fused != 0
 };
+
+// What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
+// coordinate), their previous labels, and where they sit.
+template <int D>
+struct KmBatch {
+  using Cfg = KmSmallCfg<D>;
+  f32x2 xq[Cfg::PPT][Cfg::NP > 0 ? Cfg::NP : 1];
+  float xs[Cfg::PPT];
+  int old[Cfg::PPT];
+};
+
+// Load the thread's NV vectors of round `r0` (first point index of the round) within the
+// block's chunk [.., c1).  A vector wholly inside the chunk is one 16-byte load (d = 1, 2, 4)
+// or a few 8/16-byte loads (other even d); the ragged end is read point by point.
+template <int D>
+__device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__restrict__ x,
+                                              const int32_t *__restrict__ labels, int64_t r0, int64_t c1) {
+  using Cfg = KmSmallCfg<D>;
+  constexpr int PPV = Cfg::PPV, NV = Cfg::NV, NP = Cfg::NP;
+  constexpr bool TAIL = Cfg::TAIL;
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    const int64_t i0 = r0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
+    if (i0 + PPV <= c1) {
+      const float *row = x + i0 * D;
+      if constexpr (D == 1) {
+        const float4 q = __ldg(reinterpret_cast<const float4 *>(row));
+        b.xs[v * 4 + 0] = q.x; b.xs[v * 4 + 1] = q.y; b.xs[v * 4 + 2] = q.z; b.xs[v * 4 + 3] = q.w;
+        const int4 o = *reinterpret_cast<const int4 *>(labels + i0);
+        b.old[v * 4 + 0] = o.x; b.old[v * 4 + 1] = o.y; b.old[v * 4 + 2] = o.z; b.old[v * 4 + 3] = o.w;
+      } else if constexpr (D == 2) {
+        const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row));
+        b.xq[v * 2 + 0][0] = q.x; b.xq[v * 2 + 1][0] = q.y;
+        const int2 o = *reinterpret_cast<const int2 *>(labels + i0);
+        b.old[v * 2 + 0] = o.x; b.old[v * 2 + 1] = o.y;
+      } else {
+        if constexpr (D % 4 == 0) {
+#pragma unroll
+          for (int m = 0; m < D / 4; m++) {
+            const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row) + m);
+            b.xq[v][2 * m] = q.x; b.xq[v][2 * m + 1] = q.y;
+          }
+        } else if constexpr (D % 2 == 0) {
+#pragma unroll
+          for (int m = 0; m < NP; m++) b.xq[v][m] = __ldg(reinterpret_cast<const unsigned long long *>(row) + m);
+        } else {
+#pragma unroll
+          for (int m = 0; m < NP; m++) b.xq[v][m] = pk2(__ldg(row + 2 * m), __ldg(row + 2 * m + 1));
+          b.xs[v] = __ldg(row + D - 1);
+        }
+        b.old[v] = labels[i0];
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < PPV; u++) {
+        const int64_t i = i0 + u;
+        const bool live = i < c1;
+        const int q = v * PPV + u;
+        b.old[q] = live ? labels[i] : 0;
+#pragma unroll
+        for (int m = 0; m < NP; m++)
+          b.xq[q][m] = live ? pk2(x[i * D + 2 * m], x[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
+        if (D == 1 || TAIL) b.xs[q] = live ? x[i * D + D - 1] : 0.f;
+      }
+    }
+  }
+}
 
 template <int D, bool HILO>
 __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
@@ -95,6 +164,15 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);               // optional per-block table
   const KmAccLayout L = km_acc_layout(k, D);
 
+  // this block's contiguous chunk of points, walked in rounds of THREADS*PPT
+  const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
+  const int64_t c1 = min(p.n, c0 + p.chunk);
+  constexpr int64_t per_round = (int64_t)KM_SMALL_THREADS * PPT;
+
+  // first round's loads go out before anything else so they fly while the centroids are staged
+  KmBatch<D> cur;
+  km_load_batch<D>(cur, p.x, p.labels, c0, c1);
+
   for (int e = threadIdx.x; e < k * D; e += KM_SMALL_THREADS) {
     const int jj = e / D, t = e - jj * D;
     ncf[jj * CROW + t] = -p.chi[e];
@@ -105,70 +183,19 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   T.L = L;
   T.tab = p.tab_in_smem ? stab : p.acc;
   if (p.tab_in_smem) km_tab_zero(stab, L.scal);
-  __syncthreads();
-
-  const double scale_a = p.st->scale_a, scale_b = p.st->scale_b, inertia_scale = p.st->inertia_scale;
+  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = p.st->inertia_scale;
   const float tau2 = HILO ? p.st->tau_hilo : p.st->tau_hi;   // absolute part (2.5x margin included)
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
+  __syncthreads();
+
   int changed = 0, rescored = 0;
   double inertia = 0.0;
 
-  const int64_t per_tile = (int64_t)KM_SMALL_THREADS * PPT;
-  const int64_t ntiles = (p.n + per_tile - 1) / per_tile;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t tile0 = tile * per_tile;
-    f32x2 xq[PPT][NP > 0 ? NP : 1];  // packed (x[2m], x[2m+1]) pairs, as loaded
-    float xs[PPT];                   // D == 1: the point; odd D: the last coordinate
-    int old[PPT];
-    int64_t pidx[NV];                // first point of each vector / row
-    const bool full = tile0 + per_tile <= p.n;
-#pragma unroll
-    for (int v = 0; v < NV; v++) {
-      pidx[v] = tile0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
-      if (full) {
-        const float *row = p.x + pidx[v] * D;
-        if constexpr (D == 1) {
-          const float4 q = __ldg(reinterpret_cast<const float4 *>(row));
-          xs[v * 4 + 0] = q.x; xs[v * 4 + 1] = q.y; xs[v * 4 + 2] = q.z; xs[v * 4 + 3] = q.w;
-          const int4 o = *reinterpret_cast<const int4 *>(p.labels + pidx[v]);
-          old[v * 4 + 0] = o.x; old[v * 4 + 1] = o.y; old[v * 4 + 2] = o.z; old[v * 4 + 3] = o.w;
-        } else if constexpr (D == 2) {
-          const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row));
-          xq[v * 2 + 0][0] = q.x; xq[v * 2 + 1][0] = q.y;
-          const int2 o = *reinterpret_cast<const int2 *>(p.labels + pidx[v]);
-          old[v * 2 + 0] = o.x; old[v * 2 + 1] = o.y;
-        } else {
-          if constexpr (D % 4 == 0) {
-#pragma unroll
-            for (int m = 0; m < D / 4; m++) {
-              const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row) + m);
-              xq[v][2 * m] = q.x; xq[v][2 * m + 1] = q.y;
-            }
-          } else if constexpr (D % 2 == 0) {
-#pragma unroll
-            for (int m = 0; m < NP; m++) xq[v][m] = __ldg(reinterpret_cast<const unsigned long long *>(row) + m);
-          } else {
-#pragma unroll
-            for (int m = 0; m < NP; m++) xq[v][m] = pk2(__ldg(row + 2 * m), __ldg(row + 2 * m + 1));
-            xs[v] = __ldg(row + D - 1);
-          }
-          old[v] = p.labels[pidx[v]];
-        }
-      } else {
-#pragma unroll
-        for (int u = 0; u < PPV; u++) {
-          const int64_t i = pidx[v] + u;
-          const bool live = i < p.n;
-          const int q = v * PPV + u;
-          old[q] = live ? p.labels[i] : 0;
-#pragma unroll
-          for (int m = 0; m < NP; m++)
-            xq[q][m] = live ? pk2(p.x[i * D + 2 * m], p.x[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
-          if (D == 1 || TAIL) xs[q] = live ? p.x[i * D + D - 1] : 0.f;
-        }
-      }
-    }
+  for (int64_t r0 = c0; r0 < c1; r0 += per_round) {
+    // software pipeline: the next round's loads are in flight during this round's arithmetic
+    KmBatch<D> nxt;
+    if (r0 + per_round < c1) km_load_batch<D>(nxt, p.x, p.labels, r0 + per_round, c1);
 
     // ---- binary32 filter, top-2 on integer keys
     unsigned m1[PPT], m2[PPT];
@@ -200,7 +227,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           f32x2 acc2;
 #pragma unroll
           for (int m = 0; m < NP; m++) {
-            f32x2 df = add2(xq[q][m], nh[m]);
+            f32x2 df = add2(cur.xq[q][m], nh[m]);
             if (HILO) df = add2(df, nl[m]);
             acc2 = (m == 0) ? mul2(df, df) : fma2(df, df, acc2);
           }
@@ -208,12 +235,12 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           unpk2(acc2, lo, hi);
           dist = lo + hi;
           if constexpr (TAIL) {
-            float dt = xs[q] + th;
+            float dt = cur.xs[q] + th;
             if (HILO) dt += tl;
             dist = fmaf(dt, dt, dist);
           }
         } else {
-          float dt = xs[q] + th;
+          float dt = cur.xs[q] + th;
           if (HILO) dt += tl;
           dist = dt * dt;
         }
@@ -227,14 +254,14 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     int newlab[PPT];
 #pragma unroll
     for (int q = 0; q < PPT; q++) {
-      const int64_t i = pidx[q / PPV] + (q % PPV);
-      newlab[q] = old[q];
-      if (!full && i >= p.n) continue;
+      const int64_t i = r0 + ((int64_t)(q / PPV) * KM_SMALL_THREADS + threadIdx.x) * PPV + (q % PPV);
+      newlab[q] = cur.old[q];
+      if (i >= c1) continue;
       int lab = (int)(m1[q] & mask);
       float xr[D];
 #pragma unroll
-      for (int m = 0; m < NP; m++) unpk2(xq[q][m], xr[2 * m], xr[2 * m + 1]);
-      if (D == 1 || TAIL) xr[D - 1] = xs[q];
+      for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
+      if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
       const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
       // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score
       const bool clear = (b2 - b1) > fmaf(rho2, b2, tau2);
@@ -252,9 +279,9 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       }
       inertia += best;
       newlab[q] = lab;
-      if (lab != old[q]) {
+      if (lab != cur.old[q]) {
         changed++;
-        if (p.incremental) km_move_point(T, xr, D, lab, old[q], scale_a, scale_b);
+        if (p.incremental) km_move_point(T, xr, D, lab, cur.old[q], scale_a, scale_b);
       }
       if (!p.incremental) km_move_point(T, xr, D, lab, -1, scale_a, scale_b);
     }
@@ -262,23 +289,25 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     for (int v = 0; v < NV; v++) {
       bool any = false;
 #pragma unroll
-      for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != old[v * PPV + u];
+      for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != cur.old[v * PPV + u];
       if (!any) continue;
-      if (full) {
+      const int64_t i0 = r0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
+      if (i0 + PPV <= c1) {
         if constexpr (PPV == 4) {
-          *reinterpret_cast<int4 *>(p.labels + pidx[v]) =
+          *reinterpret_cast<int4 *>(p.labels + i0) =
               make_int4(newlab[v * 4], newlab[v * 4 + 1], newlab[v * 4 + 2], newlab[v * 4 + 3]);
         } else if constexpr (PPV == 2) {
-          *reinterpret_cast<int2 *>(p.labels + pidx[v]) = make_int2(newlab[v * 2], newlab[v * 2 + 1]);
+          *reinterpret_cast<int2 *>(p.labels + i0) = make_int2(newlab[v * 2], newlab[v * 2 + 1]);
         } else {
-          p.labels[pidx[v]] = newlab[v];
+          p.labels[i0] = newlab[v];
         }
       } else {
 #pragma unroll
         for (int u = 0; u < PPV; u++)
-          if (pidx[v] + u < p.n) p.labels[pidx[v] + u] = newlab[v * PPV + u];
+          if (i0 + u < c1) p.labels[i0 + u] = newlab[v * PPV + u];
       }
     }
+    cur = nxt;
   }
 
   // ---- block epilogue: the per-thread inertia partial is made order-free here (one split
@@ -341,10 +370,19 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, KM_SMALL_THREADS, smem);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
-  const int64_t per_tile = (int64_t)KM_SMALL_THREADS * KmSmallCfg<D>::PPT;
-  const int64_t ntiles = (a.n + per_tile - 1) / per_tile;
-  const int64_t cap = (int64_t)a.sm_count * per_sm;   // one resident wave; blocks stride over tiles
-  const int grid = (int)(ntiles < cap ? ntiles : cap);
+  // balanced contiguous chunks: one resident wave of blocks, every block the same share
+  const int64_t per_round = (int64_t)KM_SMALL_THREADS * KmSmallCfg<D>::PPT;
+  const int64_t cap = (int64_t)a.sm_count * per_sm;
+  int64_t want = (a.n + per_round - 1) / per_round;
+  if (want < 1) want = 1;
+  int64_t grid64 = want < cap ? want : cap;
+  int64_t chunk = (a.n + grid64 - 1) / grid64;
+  chunk = (chunk + 3) & ~(int64_t)3;
+  grid64 = (a.n + chunk - 1) / chunk;
+  const int grid = (int)grid64;
+  p.chunk = chunk;
+  p.scale_a = a.scale_a;
+  p.scale_b = a.scale_b;
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
   (*launches)++;
   return cudaGetLastError();

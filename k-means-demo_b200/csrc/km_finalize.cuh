@@ -87,10 +87,7 @@ __device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
     s.updated = upd ? 1 : 0;
     s.pad = 0;
     for (int q = 0; q < KM_ACC_SCALARS; q++) f.acc_local[L.scal + q] = 0;
-    if (f.slot) {
-      *f.slot = s;
-      __threadfence_system();
-    }
+    if (f.slot) *f.slot = s;  // pinned host memory; visible to the host once the kernel's event completes
   }
   km_refresh_scales(f.st, cmax, f.maxabs_x, f.d);
 }

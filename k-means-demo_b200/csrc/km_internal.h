@@ -83,6 +83,7 @@ struct KmAssignArgs {
   int exact_inertia;
   int sm_count;
   int max_smem_optin;
+  double scale_a, scale_b;  // 2^qa, 2^QB (host copies of KmState's)
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmFinalizeArgs fin;  // fin.fused = 1: the assignment kernel's last block also finalizes
   cudaStream_t stream;
