@@ -249,7 +249,8 @@ def run_ours(args, wl):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
     for a, b in ev:
-        flush.zero_()            # L2 flush between timed iterations (outside the event pair)
+        if not args.no_flush:
+            flush.zero_()        # L2 flush between timed iterations (outside the event pair)
         a.record()
         st.step_async()
         b.record()
@@ -333,7 +334,7 @@ def run_ours(args, wl):
                        "seed": wl["seed"], "init": f"seeded Forgy (seed {wl['init_seed']})", "storage": "float32",
                        "arithmetic": "binary32 filter + binary64 re-score/inertia, int64 order-free sums",
                        "path": {1: "direct_f64", 2: "filter_f32", 3: "tensor"}.get(last["path_used"]),
-                       "update_mode": "incremental", "l2": "flushed between timed steps (256 MiB write)",
+                       "update_mode": "incremental", "l2": "NOT flushed (diagnostic run, invalid as a bench value)" if args.no_flush else "flushed between timed steps (256 MiB write)",
                        "timed_iterations": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} from the seeded init",
                        "changed_at_last_step": last["changed"], "parallelism": f"point-sharded x{world}"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
@@ -357,6 +358,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--run-iters", type=int, default=50)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-flush", action="store_true",
+                    help="diagnostic only: skip the L2 flush between timed steps (such a line is not a valid bench value)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -101,6 +101,9 @@ static void free_centroids(km_ctx *ctx) {
   if (ctx->acc_global && ctx->acc_global != ctx->acc) cudaFree(ctx->acc_global);
   if (ctx->acc) cudaFree(ctx->acc);
   ctx->c64 = nullptr; ctx->chi = ctx->clo = nullptr; ctx->acc = ctx->acc_global = nullptr;
+  for (int q = 0; q < 2; q++) { if (ctx->p1S[q]) cudaFree(ctx->p1S[q]); if (ctx->p1C[q]) cudaFree(ctx->p1C[q]); ctx->p1S[q] = nullptr; ctx->p1C[q] = nullptr; }
+  for (int q = 0; q < 3; q++) { if (ctx->p1D[q]) cudaFree(ctx->p1D[q]); ctx->p1D[q] = nullptr; }
+  ctx->p1 = false; ctx->p1_pending = false;
   ctx->have_centroids = false; ctx->k = 0; ctx->acc_len = 0;
 }
 
@@ -202,6 +205,12 @@ static km_status reset_labels(km_ctx *ctx) {
   if (ctx->acc) KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
   if (ctx->acc_global && ctx->acc_global != ctx->acc)
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc_global, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
+  if (ctx->p1) {
+    for (int q = 0; q < 2; q++) KM_CUDA(ctx, cudaMemsetAsync(ctx->p1S[q], 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
+    for (int q = 0; q < 3; q++) KM_CUDA(ctx, cudaMemsetAsync(ctx->p1D[q], 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
+    ctx->p1_pending = false;
+    ctx->p1_dw = 0;
+  }
   if (ctx->state) KM_CUDA(ctx, cudaMemsetAsync(&ctx->state->it, 0, sizeof(int32_t), ctx->stream));
   ctx->host_it = 0;
   ctx->labels_fresh = true;
@@ -269,7 +278,7 @@ static km_status adopt_points(km_ctx *ctx) {
   if (ctx->have_centroids) {
     if (ctx->d * (int64_t)ctx->k * 2 + ctx->k + KM_ACC_SCALARS != ctx->acc_len) {
       free_centroids(ctx);  // shape changed under the old centroids
-    } else {
+    } else if (!ctx->p1) {
       KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 0, 0), ctx->stream, &ctx->launches));
     }
   }
@@ -481,29 +490,61 @@ extern "C" km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t 
 }
 
 // ------------------------------------------------------------------ a2: initialisation
+static int pick_path_for(km_ctx *ctx, int32_t k) {
+  int want = ctx->cfg.path;
+  bool small_ok = km_small_path_supported(ctx->d, k, ctx->dtype, ctx->max_smem_optin);
+  if (want == KM_PATH_AUTO) return small_ok ? KM_PATH_FILTER_F32 : KM_PATH_DIRECT_F64;
+  return want;
+}
+
+static km_status p1_flush(km_ctx *ctx, int override_update, int override_nc);
+
 static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k) {
   const int32_t d = ctx->d;
   const KmAccLayout L = km_acc_layout(k, d);
-  if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len) {
+  const int path = pick_path_for(ctx, k);
+  if (path == KM_PATH_FILTER_F32 && !km_small_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
+    return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096, k*d <= 8192");
+  if (path == KM_PATH_TENSOR) return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR is not built yet");
+  const bool p1 = path == KM_PATH_FILTER_F32;
+  if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len || ctx->p1 != p1) {
     free_centroids(ctx);
     size_t kd = (size_t)k * d;
-    KM_CUDA(ctx, cudaMalloc(&ctx->c64, kd * sizeof(double)));
-    KM_CUDA(ctx, cudaMalloc(&ctx->chi, kd * sizeof(float)));
-    KM_CUDA(ctx, cudaMalloc(&ctx->clo, kd * sizeof(float)));
-    KM_CUDA(ctx, cudaMalloc(&ctx->acc, (size_t)L.len * sizeof(long long)));
-    if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
-    else ctx->acc_global = ctx->acc;
+    if (p1) {
+      for (int q = 0; q < 2; q++) {
+        KM_CUDA(ctx, cudaMalloc(&ctx->p1S[q], (size_t)L.len * sizeof(long long)));
+        KM_CUDA(ctx, cudaMalloc(&ctx->p1C[q], kd * sizeof(double)));
+      }
+      for (int q = 0; q < 3; q++) KM_CUDA(ctx, cudaMalloc(&ctx->p1D[q], (size_t)L.len * sizeof(long long)));
+      ctx->p1 = true;
+      ctx->p1_s = 0;
+    } else {
+      KM_CUDA(ctx, cudaMalloc(&ctx->c64, kd * sizeof(double)));
+      KM_CUDA(ctx, cudaMalloc(&ctx->chi, kd * sizeof(float)));
+      KM_CUDA(ctx, cudaMalloc(&ctx->clo, kd * sizeof(float)));
+      KM_CUDA(ctx, cudaMalloc(&ctx->acc, (size_t)L.len * sizeof(long long)));
+      if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
+      else ctx->acc_global = ctx->acc;
+    }
     ctx->k = k;
     ctx->acc_len = L.len;
     ctx->have_centroids = true;
     km_status s = reset_labels(ctx);  // k changed: old labels mean nothing
     if (s != KM_OK) return s;
   }
+  ctx->use_hilo = false;
+  if (ctx->p1) {
+    // merge whatever pass is pending under the old centroids, then overwrite them
+    km_status s = p1_flush(ctx, -1, -1);
+    if (s != KM_OK) return s;
+    KM_CUDA(ctx, cudaMemcpyAsync(ctx->p1C[ctx->p1_s], c_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // c_host is borrowed for this call only
+    return KM_OK;
+  }
   KM_CUDA(ctx, cudaMemcpyAsync(ctx->c64, c_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // c_host is borrowed for this call only
   // finalize with nothing to consume: rewrites chi/clo from c64 and refreshes the scales
   KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 0, 0), ctx->stream, &ctx->launches));
-  ctx->use_hilo = false;
   return KM_OK;
 }
 
@@ -578,18 +619,9 @@ static km_status ready(km_ctx *ctx) {
   return KM_OK;
 }
 
-static int pick_path(km_ctx *ctx) {
-  int want = ctx->cfg.path;
-  bool small_ok = km_small_path_supported(ctx->d, ctx->k, ctx->dtype, ctx->max_smem_optin);
-  if (want == KM_PATH_AUTO) return small_ok ? KM_PATH_FILTER_F32 : KM_PATH_DIRECT_F64;
-  return want;
-}
+static int pick_path(km_ctx *ctx) { return pick_path_for(ctx, ctx->k); }
 
-// One assignment pass plus its finalize.  Single rank + small-d path: the assignment
-// kernel's last block finalizes, so the whole iteration is one launch.  Otherwise the
-// NCCL all-reduce of the packed table sits between two kernels.
-static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int needs_change) {
-  KmAssignArgs a;
+static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.x = ctx->x; a.dtype = ctx->dtype; a.n = ctx->n; a.d = ctx->d; a.k = ctx->k;
   a.labels = ctx->labels; a.c64 = ctx->c64; a.chi = ctx->chi; a.clo = ctx->clo;
   a.acc = ctx->acc; a.state = ctx->state;
@@ -599,49 +631,97 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
   a.hilo = ctx->use_hilo ? 1 : 0;
   a.scale_a = ldexp(1.0, ctx->qa);
   a.scale_b = ldexp(1.0, ctx->QB);
+  memset(&a.ps, 0, sizeof(a.ps));
+}
+
+// ---- general path: assignment kernel, [NCCL all-reduce of the packed table], finalize kernel
+static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int needs_change) {
+  KmAssignArgs a;
+  fill_assign_args(ctx, a);
   const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
   if (!a.incremental)  // full mode: sums and counts are rebuilt from nothing every pass
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)L.scal * sizeof(long long), ctx->stream));
-  const int path = pick_path(ctx);
   KmStatSlot *slot = nullptr;
   if (do_stats) {
     ctx->host_it += 1;
     slot = ctx->ring_dev + (ctx->host_it % KM_RING);
   }
-  KmFinalizeArgs fin = make_fin(ctx, slot, do_stats, do_update, needs_change);
-  const bool fuse = ctx->world == 1 && path == KM_PATH_FILTER_F32 && ctx->n > 0 && do_stats &&
-                    (int64_t)ctx->k * ctx->d <= 16384;
-  fin.fused = fuse ? 1 : 0;
-  a.fin = fin;
   const bool prof = ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
   if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
-  switch (path) {
-    case KM_PATH_DIRECT_F64:
-      KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
-      break;
-    case KM_PATH_FILTER_F32:
-      if (!km_small_path_supported(ctx->d, ctx->k, ctx->dtype, ctx->max_smem_optin))
-        return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096 and room for the centroids in shared memory");
-      KM_CUDA(ctx, km_launch_assign_small(a, &ctx->launches));
-      break;
-    default:
-      return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR is not built yet");
-  }
-  ctx->last_path = path;
+  KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
+  ctx->last_path = KM_PATH_DIRECT_F64;
   if (prof) {
     KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][1], ctx->stream));
     ctx->prof_n++;
   }
   ctx->labels_fresh = false;
-  if (!fuse) {
-    if (ctx->world > 1)
-      KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
-                                     ctx->nccl_comm, ctx->stream));
-    fin.fused = 0;
-    KM_CUDA(ctx, km_launch_finalize(fin, ctx->stream, &ctx->launches));
-  }
+  if (ctx->world > 1)
+    KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
+                                   ctx->nccl_comm, ctx->stream));
+  KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, slot, do_stats, do_update, needs_change), ctx->stream, &ctx->launches));
   if (do_stats) KM_CUDA(ctx, cudaEventRecord(ctx->ring_ev[ctx->host_it % KM_RING], ctx->stream));
   return KM_OK;
+}
+
+// ---- small-d path, prologue-finalize protocol.  One launch per pass:
+// the kernel's prologue merges the pending pass's deltas into the sums, derives the
+// centroids, publishes the pending pass's stats; then it assigns this rank's points and
+// leaves its own deltas pending.  `assign` = false runs the prologue alone (n = 0).
+static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
+  KmAssignArgs a;
+  fill_assign_args(ctx, a);
+  if (!assign) a.n = 0;
+  KmPass &ps = a.ps;
+  const int s = ctx->p1_s;
+  ps.S_in = ctx->p1S[s]; ps.S_out = ctx->p1S[s ^ 1];
+  ps.C_in = ctx->p1C[s]; ps.C_out = ctx->p1C[s ^ 1];
+  ps.D_in = ctx->p1_pending ? ctx->p1D[ctx->p1_dpend] : nullptr;
+  ps.D_out = ctx->p1D[ctx->p1_dw];
+  ps.D_zero = assign ? ctx->p1D[(ctx->p1_dw + 1) % 3] : nullptr;
+  ps.slot = ctx->p1_pending ? ctx->ring_dev + (ctx->p1_pend_it % KM_RING) : nullptr;
+  ps.it_pending = ctx->p1_pend_it;
+  ps.full_mode = a.incremental ? 0 : 1;
+  ps.apply_update = update;
+  ps.needs_change = nc;
+  ps.QB = ctx->QB; ps.qa = ctx->qa; ps.maxabs_x = ctx->maxabs;
+  const bool prof = assign && ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
+  if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
+  KM_CUDA(ctx, km_launch_assign_small(a, &ctx->launches));
+  if (prof) {
+    KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][1], ctx->stream));
+    ctx->prof_n++;
+  }
+  if (ctx->p1_pending) KM_CUDA(ctx, cudaEventRecord(ctx->ring_ev[ctx->p1_pend_it % KM_RING], ctx->stream));
+  ctx->p1_s = s ^ 1;
+  ctx->p1_pending = false;
+  ctx->last_path = KM_PATH_FILTER_F32;
+  if (assign) {
+    if (ctx->world > 1)  // the one collective of an iteration: the packed deltas, in place
+      KM_NCCL(ctx, g_nccl.all_reduce(ps.D_out, ps.D_out, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
+                                     ctx->nccl_comm, ctx->stream));
+    ctx->host_it += 1;
+    ctx->p1_pending = true;
+    ctx->p1_dpend = ctx->p1_dw;
+    ctx->p1_dw = (ctx->p1_dw + 1) % 3;
+    ctx->p1_pend_it = ctx->host_it;
+    ctx->labels_fresh = false;
+  }
+  return KM_OK;
+}
+
+// an assignment pass; the pass pending before it is merged with the intent it was issued with
+static km_status p1_assign(km_ctx *ctx, int intent_update, int intent_nc) {
+  km_status s = p1_launch(ctx, true, ctx->p1_pending ? ctx->p1_pend_update : 0, ctx->p1_pending ? ctx->p1_pend_nc : 0);
+  ctx->p1_pend_update = intent_update;
+  ctx->p1_pend_nc = intent_nc;
+  return s;
+}
+
+// merge the pending pass now (prologue-only launch); -1 keeps the intent it was issued with
+static km_status p1_flush(km_ctx *ctx, int override_update, int override_nc) {
+  if (!ctx->p1 || !ctx->p1_pending) return KM_OK;
+  return p1_launch(ctx, false, override_update < 0 ? ctx->p1_pend_update : override_update,
+                   override_nc < 0 ? ctx->p1_pend_nc : override_nc);
 }
 
 static void fill_stats(km_ctx *ctx, const KmStatSlot &s, km_stats *out, float ms) {
@@ -671,7 +751,10 @@ extern "C" km_status km_assign(km_ctx *ctx, km_stats *stats) {
   km_status s = ready(ctx);
   if (s != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  if ((s = enqueue_pass(ctx, 1, 0, 0)) != KM_OK) return s;
+  if (ctx->p1) {
+    if ((s = p1_assign(ctx, 0, 0)) != KM_OK) return s;
+    if ((s = p1_flush(ctx, -1, -1)) != KM_OK) return s;
+  } else if ((s = enqueue_pass(ctx, 1, 0, 0)) != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KmStatSlot slot;
   if ((s = wait_slot(ctx, ctx->host_it, &slot)) != KM_OK) return s;
@@ -688,7 +771,13 @@ extern "C" km_status km_update(km_ctx *ctx, km_stats *stats) {
   if (s != KM_OK) return s;
   if (ctx->labels_fresh) return fail(ctx, KM_ERR_STATE, "km_update: nothing assigned yet");
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 1, 0), ctx->stream, &ctx->launches));
+  if (ctx->p1) {
+    if (ctx->p1_pending) s = p1_flush(ctx, 1, 0);
+    else s = p1_launch(ctx, false, 1, 0);
+    if (s != KM_OK) return s;
+  } else {
+    KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, nullptr, 0, 1, 0), ctx->stream, &ctx->launches));
+  }
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
   if (stats) {
@@ -704,14 +793,16 @@ extern "C" km_status km_step_async(km_ctx *ctx) {
   KM_BIND(ctx);
   km_status s = ready(ctx);
   if (s != KM_OK) return s;
-  return enqueue_pass(ctx, 1, 1, 1);
+  return ctx->p1 ? p1_assign(ctx, 1, 1) : enqueue_pass(ctx, 1, 1, 1);
 }
 
 extern "C" km_status km_stats_fetch(km_ctx *ctx, km_stats *stats) {
   KM_BIND(ctx);
   if (ctx->host_it == 0) return fail(ctx, KM_ERR_STATE, "km_stats_fetch: no step issued");
   KmStatSlot slot;
-  km_status s = wait_slot(ctx, ctx->host_it, &slot);
+  km_status s = p1_flush(ctx, -1, -1);
+  if (s != KM_OK) return s;
+  s = wait_slot(ctx, ctx->host_it, &slot);
   if (s != KM_OK) return s;
   fill_stats(ctx, slot, stats, 0.f);
   return KM_OK;
@@ -723,6 +814,7 @@ extern "C" km_status km_step(km_ctx *ctx, km_stats *stats) {
   if (s != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   if ((s = km_step_async(ctx)) != KM_OK) return s;
+  if ((s = p1_flush(ctx, -1, -1)) != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KmStatSlot slot;
   if ((s = wait_slot(ctx, ctx->host_it, &slot)) != KM_OK) return s;
@@ -760,18 +852,24 @@ extern "C" km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats) {
     while (issued < max_iter && issued - checked < KM_RUN_LAG + 1) {
       issued++;
       // the update after the max_iter-th assign never happens (A5)
-      if ((s = enqueue_pass(ctx, 1, issued < max_iter, 1)) != KM_OK) return s;
+      s = ctx->p1 ? p1_assign(ctx, issued < max_iter, 1) : enqueue_pass(ctx, 1, issued < max_iter, 1);
+      if (s != KM_OK) return s;
     }
+    // small-d path: pass t's stats are published by pass t+1's prologue; the newest pass
+    // needs an explicit merge
+    if (ctx->p1 && checked + 1 == issued && (s = p1_flush(ctx, -1, -1)) != KM_OK) return s;
     if ((s = wait_slot(ctx, checked + 1, &last)) != KM_OK) return s;
     checked++;
     if (last.changed == 0 || checked == max_iter) done = true;
   }
+  if ((s = p1_flush(ctx, -1, -1)) != KM_OK) return s;  // speculative passes past the answer change nothing
   KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));  // drains the speculative passes too
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
   // speculative passes ran past the answer: rewind the iteration counters to it
   ctx->host_it = checked;
+  ctx->p1_pend_it = checked;
   KM_CUDA(ctx, cudaMemcpyAsync(&ctx->state->it, &ctx->host_it, sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
   KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->ring[checked % KM_RING] = last;
@@ -790,15 +888,18 @@ extern "C" km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n) {
 extern "C" km_status km_get_centroids(km_ctx *ctx, double *out) {
   KM_BIND(ctx);
   if (!ctx->have_centroids || !out) return fail(ctx, KM_ERR_STATE, "no centroids");
-  return copy_d2h(ctx, out, ctx->c64, (size_t)ctx->k * ctx->d * sizeof(double));
+  km_status s = p1_flush(ctx, -1, -1);
+  if (s != KM_OK) return s;
+  return copy_d2h(ctx, out, ctx->p1 ? ctx->p1C[ctx->p1_s] : ctx->c64, (size_t)ctx->k * ctx->d * sizeof(double));
 }
 
 static km_status fetch_acc(km_ctx *ctx, std::vector<long long> &h) {
   if (!ctx->have_centroids) return fail(ctx, KM_ERR_STATE, "no centroids");
   h.resize((size_t)ctx->acc_len);
-  // in incremental mode the local table is always current; the all-reduced copy is as of
-  // the last assign, which is what "the whole job" means
-  return copy_d2h(ctx, h.data(), ctx->acc_global, h.size() * sizeof(long long));
+  km_status s = p1_flush(ctx, -1, -1);
+  if (s != KM_OK) return s;
+  // whole-job sums as of the last assign (the all-reduced copy when world > 1)
+  return copy_d2h(ctx, h.data(), ctx->p1 ? ctx->p1S[ctx->p1_s] : ctx->acc_global, h.size() * sizeof(long long));
 }
 
 extern "C" km_status km_get_counts(km_ctx *ctx, int64_t *out) {

@@ -17,9 +17,11 @@
 //     labels are the oracle's bit for bit at binary32 cost;
 //   * label compare, move of re-labelled points between the order-free per-cluster sums,
 //     change count and inertia are fused into the same pass: x is read once per iteration;
-//   * optionally the last block to finish also performs the centroid update (finalize), so
-//     a Lloyd iteration is ONE kernel launch.
-#include <cuda_fp16.h>
+//   * the centroid update is folded into the NEXT pass's prologue: every block rebuilds the
+//     centroids from the order-free sums (k*d divisions — nothing next to its share of the
+//     points), so a Lloyd iteration is ONE kernel launch with no grid-wide hand-off, no
+//     last-block tail and, across GPUs, one all-reduce and nothing else.
+#include <type_traits>
 
 #include "km_commit.cuh"
 #include "km_finalize.cuh"
@@ -68,11 +70,6 @@ struct KmSmallParams {
   int64_t n;
   int32_t k;
   int32_t *labels;
-  const double *c64;
-  const float *chi;
-  const float *clo;
-  long long *acc;
-  KmState *st;
   int incremental;
   int exact_inertia;
   int tab_in_smem;
@@ -80,7 +77,7 @@ struct KmSmallParams {
   float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
   int64_t chunk;       // points per block (multiple of 4)
-  KmFinalizeArgs fin;  // used when fin.fused != 0
+  KmPass ps;           // sums / centroids / deltas this pass reads and writes
 };
 
 // What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
@@ -97,25 +94,25 @@ struct KmBatch {
 // block's chunk [.., c1).  A vector wholly inside the chunk is one 16-byte load (d = 1, 2, 4)
 // or a few 8/16-byte loads (other even d); the ragged end is read point by point.
 template <int D>
-__device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__restrict__ x,
-                                              const int32_t *__restrict__ labels, int64_t r0, int64_t c1) {
+__device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__restrict__ xb,
+                                              const int32_t *__restrict__ lb, int r, int cn) {
   using Cfg = KmSmallCfg<D>;
   constexpr int PPV = Cfg::PPV, NV = Cfg::NV, NP = Cfg::NP;
   constexpr bool TAIL = Cfg::TAIL;
 #pragma unroll
   for (int v = 0; v < NV; v++) {
-    const int64_t i0 = r0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
-    if (i0 + PPV <= c1) {
-      const float *row = x + i0 * D;
+    const int i0 = r + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;   // offset within the chunk
+    if (i0 + PPV <= cn) {
+      const float *row = xb + i0 * D;
       if constexpr (D == 1) {
         const float4 q = __ldg(reinterpret_cast<const float4 *>(row));
         b.xs[v * 4 + 0] = q.x; b.xs[v * 4 + 1] = q.y; b.xs[v * 4 + 2] = q.z; b.xs[v * 4 + 3] = q.w;
-        const int4 o = *reinterpret_cast<const int4 *>(labels + i0);
+        const int4 o = *reinterpret_cast<const int4 *>(lb + i0);
         b.old[v * 4 + 0] = o.x; b.old[v * 4 + 1] = o.y; b.old[v * 4 + 2] = o.z; b.old[v * 4 + 3] = o.w;
       } else if constexpr (D == 2) {
         const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row));
         b.xq[v * 2 + 0][0] = q.x; b.xq[v * 2 + 1][0] = q.y;
-        const int2 o = *reinterpret_cast<const int2 *>(labels + i0);
+        const int2 o = *reinterpret_cast<const int2 *>(lb + i0);
         b.old[v * 2 + 0] = o.x; b.old[v * 2 + 1] = o.y;
       } else {
         if constexpr (D % 4 == 0) {
@@ -132,19 +129,19 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
           for (int m = 0; m < NP; m++) b.xq[v][m] = pk2(__ldg(row + 2 * m), __ldg(row + 2 * m + 1));
           b.xs[v] = __ldg(row + D - 1);
         }
-        b.old[v] = labels[i0];
+        b.old[v] = lb[i0];
       }
     } else {
 #pragma unroll
       for (int u = 0; u < PPV; u++) {
-        const int64_t i = i0 + u;
-        const bool live = i < c1;
+        const int i = i0 + u;
+        const bool live = i < cn;
         const int q = v * PPV + u;
-        b.old[q] = live ? labels[i] : 0;
+        b.old[q] = live ? lb[i] : 0;
 #pragma unroll
         for (int m = 0; m < NP; m++)
-          b.xq[q][m] = live ? pk2(x[i * D + 2 * m], x[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
-        if (D == 1 || TAIL) b.xs[q] = live ? x[i * D + D - 1] : 0.f;
+          b.xq[q][m] = live ? pk2(xb[i * D + 2 * m], xb[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
+        if (D == 1 || TAIL) b.xs[q] = live ? xb[i * D + D - 1] : 0.f;
       }
     }
   }
@@ -163,39 +160,108 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   double *cd = reinterpret_cast<double *>(ncf + (((size_t)k * CROW + 3) & ~(size_t)3));  // [k][D] binary64 masters
   long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);               // optional per-block table
   const KmAccLayout L = km_acc_layout(k, D);
+  const KmPass &ps = p.ps;
 
-  // this block's contiguous chunk of points, walked in rounds of THREADS*PPT
+  // this block's contiguous chunk of points, walked in rounds of THREADS*PPT; everything
+  // inside the chunk is addressed with 32-bit offsets from the chunk's base
   const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
-  const int64_t c1 = min(p.n, c0 + p.chunk);
-  constexpr int64_t per_round = (int64_t)KM_SMALL_THREADS * PPT;
+  const int cn = (int)max((int64_t)0, min(p.n - c0, p.chunk));
+  const float *__restrict__ xb = p.x + c0 * D;
+  int32_t *__restrict__ lb = p.labels + c0;
+  constexpr int per_round = KM_SMALL_THREADS * PPT;
 
-  // first round's loads go out before anything else so they fly while the centroids are staged
+  // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
-  km_load_batch<D>(cur, p.x, p.labels, c0, c1);
+  km_load_batch<D>(cur, xb, lb, 0, cn);
 
+  // ---- prologue = the previous pass's centroid update (a4), redone by every block:
+  //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
+  //   centroid  c = S / count where the update applies and count > 0, else C_in (A4: an
+  //             empty cluster keeps its centroid, /root/reference/app.mjs:322,484-488)
+  // Block 0 also writes S and c back (S_out, C_out), publishes the pending pass's stats
+  // and clears the delta table of the pass after this one.
+  const bool pend = ps.D_in != nullptr;
+  const long long changed_prev = pend ? ps.D_in[L.scal + KM_ACC_CHANGED] : 0;
+  const bool upd = ps.apply_update && (!ps.needs_change || changed_prev > 0);
+  double cmax_in = 0.0, cmax_new = 0.0;
   for (int e = threadIdx.x; e < k * D; e += KM_SMALL_THREADS) {
     const int jj = e / D, t = e - jj * D;
-    ncf[jj * CROW + t] = -p.chi[e];
-    if (HILO) ncf[jj * CROW + D + t] = -p.clo[e];
-    cd[e] = p.c64[e];
+    long long sa = ps.S_in[L.sa + e], sb = ps.S_in[L.sb + e], cn = ps.S_in[L.cnt + jj];
+    if (pend) {
+      const long long da = ps.D_in[L.sa + e], db = ps.D_in[L.sb + e], dc = ps.D_in[L.cnt + jj];
+      if (ps.full_mode) { sa = da; sb = db; cn = dc; } else { sa += da; sb += db; cn += dc; }
+    }
+    const double cin = ps.C_in[e];
+    double c = cin;
+    if (upd && cn > 0) c = __ddiv_rn(km_fixed_to_double(sa, sb, ps.QB, ps.qa + ps.QB), (double)cn);
+    const float h = __double2float_rn(c);
+    ncf[jj * CROW + t] = -h;
+    if (HILO) ncf[jj * CROW + D + t] = -__double2float_rn(__dsub_rn(c, (double)h));
+    cd[e] = c;
+    if (blockIdx.x == 0) {
+      ps.S_out[L.sa + e] = sa;
+      ps.S_out[L.sb + e] = sb;
+      if (t == 0) ps.S_out[L.cnt + jj] = cn;
+      ps.C_out[e] = c;
+    }
+    cmax_in = fmax(cmax_in, fabs(cin));
+    cmax_new = fmax(cmax_new, fabs(c));
   }
+  __shared__ double s_red[2][KM_SMALL_THREADS / 32];
+  __shared__ double s_iscale;
+  __shared__ float s_tau;
+  __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, inertia limbs, rescored
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int red_warps = min(KM_SMALL_THREADS / 32, (k * D + 31) / 32);   // warps that saw an element
+  if (warp < red_warps) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      cmax_in = fmax(cmax_in, __shfl_xor_sync(0xffffffffu, cmax_in, o));
+      cmax_new = fmax(cmax_new, __shfl_xor_sync(0xffffffffu, cmax_new, o));
+    }
+    if (lane == 0) { s_red[0][warp] = cmax_in; s_red[1][warp] = cmax_new; }
+  }
+  if (threadIdx.x < KM_ACC_SCALARS) s_scal[threadIdx.x] = 0;
   KmBlockTab T;
   T.L = L;
-  T.tab = p.tab_in_smem ? stab : p.acc;
+  T.tab = p.tab_in_smem ? stab : ps.D_out;
   if (p.tab_in_smem) km_tab_zero(stab, L.scal);
-  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = p.st->inertia_scale;
-  const float tau2 = HILO ? p.st->tau_hilo : p.st->tau_hi;   // absolute part (2.5x margin included)
+  if (blockIdx.x == 0 && ps.D_zero)
+    for (int e = threadIdx.x; e < (int)L.len; e += KM_SMALL_THREADS) ps.D_zero[e] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double mi = 0.0, mn = 0.0;
+    for (int w = 0; w < red_warps; w++) { mi = fmax(mi, s_red[0][w]); mn = fmax(mn, s_red[1][w]); }
+    const KmScales sc = km_scales_from_cmax(mn, ps.maxabs_x, D, ps.QB);
+    s_iscale = sc.inertia_scale;
+    s_tau = HILO ? sc.tau_hilo : sc.tau_hi;
+    if (blockIdx.x == 0 && pend && ps.slot) {
+      // the pending pass ran under the scales of C_in
+      const KmScales si = km_scales_from_cmax(mi, ps.maxabs_x, D, ps.QB);
+      KmStatSlot sl;
+      sl.it = ps.it_pending;
+      sl.changed = changed_prev;
+      sl.inertia = km_fixed_to_double(ps.D_in[L.scal + KM_ACC_INERTIA_A], ps.D_in[L.scal + KM_ACC_INERTIA_B], ps.QB,
+                                      si.qi + ps.QB);
+      sl.rescored = ps.D_in[L.scal + KM_ACC_RESCORED];
+      sl.updated = upd ? 1 : 0;
+      sl.pad = 0;
+      *ps.slot = sl;   // pinned host memory; visible once this kernel's event completes
+    }
+  }
+  __syncthreads();
+  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = s_iscale;
+  const float tau2 = s_tau;   // absolute part of the ambiguity threshold (2.5x margin included)
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
-  __syncthreads();
 
   int changed = 0, rescored = 0;
   double inertia = 0.0;
 
-  for (int64_t r0 = c0; r0 < c1; r0 += per_round) {
+  for (int r0 = 0; r0 < cn; r0 += per_round) {
     // software pipeline: the next round's loads are in flight during this round's arithmetic
     KmBatch<D> nxt;
-    if (r0 + per_round < c1) km_load_batch<D>(nxt, p.x, p.labels, r0 + per_round, c1);
+    if (r0 + per_round < cn) km_load_batch<D>(nxt, xb, lb, r0 + per_round, cn);
 
     // ---- binary32 filter, top-2 on integer keys
     unsigned m1[PPT], m2[PPT];
@@ -250,87 +316,93 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       }
     }
 
-    // ---- per point: ambiguity test, rare binary64 re-score, inertia, commit
-    int newlab[PPT];
+    // ---- per point: ambiguity test, rare binary64 re-score, inertia, commit.  A round that
+    // lies wholly inside the chunk takes the copy with no bounds checks.
+    auto tail = [&](auto full_tag) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      int newlab[PPT];
 #pragma unroll
-    for (int q = 0; q < PPT; q++) {
-      const int64_t i = r0 + ((int64_t)(q / PPV) * KM_SMALL_THREADS + threadIdx.x) * PPV + (q % PPV);
-      newlab[q] = cur.old[q];
-      if (i >= c1) continue;
-      int lab = (int)(m1[q] & mask);
-      float xr[D];
-#pragma unroll
-      for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
-      if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
-      const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
-      // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score
-      const bool clear = (b2 - b1) > fmaf(rho2, b2, tau2);
-      double best;
-      if (!clear) {
-        rescored++;
-        best = __longlong_as_double(0x7FF0000000000000LL);
-        lab = 0;
-        for (int j = 0; j < k; j++) {
-          const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
-          if (dj < best) { best = dj; lab = j; }
+      for (int q = 0; q < PPT; q++) {
+        newlab[q] = cur.old[q];
+        if (!FULL) {
+          const int i = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV);
+          if (i >= cn) continue;
         }
-      } else {
-        best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
-      }
-      inertia += best;
-      newlab[q] = lab;
-      if (lab != cur.old[q]) {
-        changed++;
-        if (p.incremental) km_move_point(T, xr, D, lab, cur.old[q], scale_a, scale_b);
-      }
-      if (!p.incremental) km_move_point(T, xr, D, lab, -1, scale_a, scale_b);
-    }
+        int lab = (int)(m1[q] & mask);
+        float xr[D];
 #pragma unroll
-    for (int v = 0; v < NV; v++) {
-      bool any = false;
-#pragma unroll
-      for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != cur.old[v * PPV + u];
-      if (!any) continue;
-      const int64_t i0 = r0 + ((int64_t)v * KM_SMALL_THREADS + threadIdx.x) * PPV;
-      if (i0 + PPV <= c1) {
-        if constexpr (PPV == 4) {
-          *reinterpret_cast<int4 *>(p.labels + i0) =
-              make_int4(newlab[v * 4], newlab[v * 4 + 1], newlab[v * 4 + 2], newlab[v * 4 + 3]);
-        } else if constexpr (PPV == 2) {
-          *reinterpret_cast<int2 *>(p.labels + i0) = make_int2(newlab[v * 2], newlab[v * 2 + 1]);
+        for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
+        if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
+        const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
+        // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score
+        const bool clear = (b2 - b1) > fmaf(rho2, b2, tau2);
+        double best;
+        if (!clear) {
+          rescored++;
+          best = __longlong_as_double(0x7FF0000000000000LL);
+          lab = 0;
+          for (int j = 0; j < k; j++) {
+            const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
+            if (dj < best) { best = dj; lab = j; }
+          }
         } else {
-          p.labels[i0] = newlab[v];
+          best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
         }
-      } else {
-#pragma unroll
-        for (int u = 0; u < PPV; u++)
-          if (i0 + u < c1) p.labels[i0 + u] = newlab[v * PPV + u];
+        inertia += best;
+        newlab[q] = lab;
+        if (lab != cur.old[q]) {
+          changed++;
+          if (p.incremental) km_move_point(T, xr, D, lab, cur.old[q], scale_a, scale_b);
+        }
+        if (!p.incremental) km_move_point(T, xr, D, lab, -1, scale_a, scale_b);
       }
-    }
+#pragma unroll
+      for (int v = 0; v < NV; v++) {
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != cur.old[v * PPV + u];
+        if (!any) continue;
+        const int i0 = r0 + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;
+        if (FULL || i0 + PPV <= cn) {
+          if constexpr (PPV == 4) {
+            *reinterpret_cast<int4 *>(lb + i0) =
+                make_int4(newlab[v * 4], newlab[v * 4 + 1], newlab[v * 4 + 2], newlab[v * 4 + 3]);
+          } else if constexpr (PPV == 2) {
+            *reinterpret_cast<int2 *>(lb + i0) = make_int2(newlab[v * 2], newlab[v * 2 + 1]);
+          } else {
+            lb[i0] = newlab[v];
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < PPV; u++)
+            if (i0 + u < cn) lb[i0 + u] = newlab[v * PPV + u];
+        }
+      }
+    };
+    if (r0 + per_round <= cn) tail(std::true_type{}); else tail(std::false_type{});
     cur = nxt;
   }
 
-  // ---- block epilogue: the per-thread inertia partial is made order-free here (one split
-  // per thread), everything beyond this point is integer adds
-  KmThreadScalars S;
-  S.changed = changed;
-  S.rescored = rescored;
-  km_fixed_split(inertia, inertia_scale, scale_b, S.ia, S.ib);
-  __syncthreads();
-  if (p.tab_in_smem) km_tab_flush(stab, p.acc, L.scal);
-  km_flush_scalars(S, p.acc, L);
-  if (p.fin.fused) {
-    __shared__ int is_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicAdd(&p.st->ticket, 1u) == gridDim.x - 1);
-    __syncthreads();
-    if (is_last) {
-      __threadfence();
-      if (threadIdx.x == 0) p.st->ticket = 0;
-      km_finalize_block(p.fin);
+  // ---- block epilogue.  Counts go through one REDUX per warp; the inertia partial is summed
+  // across the warp in binary64 and made order-free there (one split per warp), so every
+  // add beyond this point is an integer add.
+  {
+    const int wc = __reduce_add_sync(0xffffffffu, changed), wr = __reduce_add_sync(0xffffffffu, rescored);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) inertia += __shfl_xor_sync(0xffffffffu, inertia, o);
+    if (lane == 0) {
+      long long ia, ib;
+      km_fixed_split(inertia, inertia_scale, scale_b, ia, ib);
+      if (wc) km_atomic_add_ll(&s_scal[KM_ACC_CHANGED], wc);
+      if (wr) km_atomic_add_ll(&s_scal[KM_ACC_RESCORED], wr);
+      km_atomic_add_ll(&s_scal[KM_ACC_INERTIA_A], ia);
+      km_atomic_add_ll(&s_scal[KM_ACC_INERTIA_B], ib);
     }
   }
+  __syncthreads();
+  if (p.tab_in_smem) km_tab_flush(stab, ps.D_out, L.scal);
+  if (threadIdx.x < KM_ACC_SCALARS && s_scal[threadIdx.x] != 0)
+    km_atomic_add_ll(ps.D_out + L.scal + threadIdx.x, s_scal[threadIdx.x]);
 }
 
 static size_t small_centroid_smem(int32_t d, int32_t k, bool hilo) {
@@ -340,6 +412,7 @@ static size_t small_centroid_smem(int32_t d, int32_t k, bool hilo) {
 
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin) {
   if (dtype != KM_DTYPE_F32 || d < 1 || d > 8 || k > 4096) return false;
+  if ((int64_t)k * d > 8192) return false;   // every block rebuilds the centroids in its prologue
   return small_centroid_smem(d, k, true) + 4096 <= (size_t)max_smem_optin / 2;
 }
 
@@ -349,8 +422,8 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   size_t smem = small_centroid_smem(D, a.k, HILO);
   KmSmallParams p;
   p.x = (const float *)a.x; p.n = a.n; p.k = a.k; p.labels = a.labels;
-  p.c64 = a.c64; p.chi = a.chi; p.clo = a.clo; p.acc = a.acc; p.st = a.state;
   p.incremental = a.incremental; p.exact_inertia = a.exact_inertia;
+  p.ps = a.ps;
   p.tab_in_smem = 0;
   const size_t tab_bytes = (size_t)L.scal * sizeof(long long);
   if (tab_bytes <= 48 * 1024 && smem + tab_bytes + 4096 <= (size_t)a.max_smem_optin / 2) {
@@ -362,7 +435,6 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   p.key_mask = (1u << bits) - 1u;
   // (D+6) u for the arithmetic, 2^-(23-bits) for the key truncation, x2.5 margin
   p.rho2 = 2.5f * ((float)(D + 6) * 0x1.0p-24f + ldexpf(1.0f, bits - 23));
-  p.fin = a.fin;
   auto kern = km_assign_small_kernel<D, HILO>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -378,7 +450,11 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   int64_t grid64 = want < cap ? want : cap;
   int64_t chunk = (a.n + grid64 - 1) / grid64;
   chunk = (chunk + 3) & ~(int64_t)3;
+  if (chunk < 4) chunk = 4;
+  const int64_t max_chunk = ((int64_t)1 << 30) / D;   // 32-bit offsets inside a chunk
+  if (chunk > max_chunk) chunk = max_chunk & ~(int64_t)3;
   grid64 = (a.n + chunk - 1) / chunk;
+  if (grid64 < 1) grid64 = 1;   // n == 0: one block still runs the prologue (publish / update)
   const int grid = (int)grid64;
   p.chunk = chunk;
   p.scale_a = a.scale_a;
@@ -404,7 +480,6 @@ static cudaError_t dispatch_small(const KmAssignArgs &a, int64_t *launches) {
 }
 
 cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches) {
-  if (a.n == 0 && !a.fin.fused) return cudaSuccess;
   if ((reinterpret_cast<uintptr_t>(a.x) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15))
     return cudaErrorMisalignedAddress;
   return a.hilo ? dispatch_small<true>(a, launches) : dispatch_small<false>(a, launches);

@@ -51,6 +51,27 @@ struct KmState {
   unsigned long long cmax_bits;  // scratch for the finalize kernel's max reduction
 };
 
+// Small-d path ("prologue-finalize" protocol): what one pass reads and writes.
+// Every launch reads (S_in, C_in) plus the pending pass's deltas D_in, and block 0 writes the
+// merged sums and the centroids it derived to (S_out, C_out).  Points are accumulated into
+// D_out; D_zero is the table the pass after this one will accumulate into.
+struct KmPass {
+  const long long *S_in;
+  long long *S_out;
+  const double *C_in;
+  double *C_out;
+  const long long *D_in;   // nullptr: no pass pending
+  long long *D_out;
+  long long *D_zero;       // may be nullptr
+  struct KmStatSlot *slot; // where block 0 publishes the pending pass's stats (or nullptr)
+  long long it_pending;
+  int full_mode;           // D_in holds complete sums, not deltas
+  int apply_update;        // derive centroids from the sums ...
+  int needs_change;        // ... only if the pending pass changed a label
+  int QB, qa;
+  double maxabs_x;
+};
+
 // One slot of the pinned-host stats ring the finalize kernel writes.
 struct KmStatSlot {
   long long it;

@@ -27,19 +27,32 @@ struct KmFinalizeArgs {
 __device__ __forceinline__ int km_bitlen(int v) { return 32 - __clz(v); }
 
 // Filter error terms and the inertia scale follow the current centroids.
-__device__ __forceinline__ void km_refresh_scales(KmState *st, double cmax, double maxabs_x, int d) {
+struct KmScales {
+  int qi;
+  double inertia_scale;
+  float tau_hilo, tau_hi;
+};
+__device__ __forceinline__ KmScales km_scales_from_cmax(double cmax, double maxabs_x, int d, int QB) {
+  KmScales r;
   double M = fmax(cmax, maxabs_x);
   int EM = (M > 0.0) ? (ilogb(M) + 1) : 0;
   int Ei = 2 * EM + 2 + km_bitlen(d);
-  int qi = st->QB - Ei;
-  st->qi = qi;
-  st->inertia_scale = scalbn(1.0, qi);
-  st->cmax = cmax;
+  r.qi = QB - Ei;
+  r.inertia_scale = scalbn(1.0, r.qi);
   double c2 = cmax * cmax;
   double t_hilo = 2.5 * (4.2 * (double)d * 0x1.0p-72 * c2) + (double)d * 0x1.0p-140;
   double t_hi = 2.5 * (1.01 * (double)d * 0x1.0p-24 * c2) + (double)d * 0x1.0p-140;
-  st->tau_hilo = __double2float_ru(t_hilo);
-  st->tau_hi = __double2float_ru(t_hi);
+  r.tau_hilo = __double2float_ru(t_hilo);
+  r.tau_hi = __double2float_ru(t_hi);
+  return r;
+}
+__device__ __forceinline__ void km_refresh_scales(KmState *st, double cmax, double maxabs_x, int d) {
+  const KmScales r = km_scales_from_cmax(cmax, maxabs_x, d, st->QB);
+  st->qi = r.qi;
+  st->inertia_scale = r.inertia_scale;
+  st->cmax = cmax;
+  st->tau_hilo = r.tau_hilo;
+  st->tau_hi = r.tau_hi;
 }
 
 // All threads of exactly one block call this.

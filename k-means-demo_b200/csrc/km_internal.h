@@ -63,6 +63,18 @@ struct km_ctx {
   cudaEvent_t prof_ev[KM_PROF_RING][2];
   int prof_n = 0;
 
+  // ---- small-d path, prologue-finalize protocol
+  bool p1 = false;
+  long long *p1S[2] = {nullptr, nullptr};  // merged sums + counts (ping-pong)
+  double *p1C[2] = {nullptr, nullptr};     // centroids (ping-pong)
+  long long *p1D[3] = {nullptr, nullptr, nullptr};  // per-pass delta tables (+ scalars), rotating
+  int p1_s = 0;            // current S / C index
+  int p1_dw = 0;           // delta table the next pass writes (zero by invariant)
+  bool p1_pending = false; // a pass's deltas await merging (and its stats publishing)
+  int p1_dpend = 0;        // ... in this table
+  int p1_pend_update = 0, p1_pend_nc = 0;  // ... to be applied with this intent
+  int32_t p1_pend_it = 0;
+
   // ---- multi-GPU
   int rank = 0, world = 1;
   void *nccl_comm = nullptr;
@@ -85,7 +97,7 @@ struct KmAssignArgs {
   int max_smem_optin;
   double scale_a, scale_b;  // 2^qa, 2^QB (host copies of KmState's)
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
-  KmFinalizeArgs fin;  // fin.fused = 1: the assignment kernel's last block also finalizes
+  KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
   cudaStream_t stream;
 };
 
