@@ -165,6 +165,35 @@ KM_API km_status km_get_balance(km_ctx *ctx, int64_t *max_out, int64_t *min_out,
  * parameters {E, NB, QB, qa} (for bit-level parity tests) */
 KM_API km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t params4[4]);
 
+/* ---- for hosts that may not allocate --------------------------------------------------- */
+/* No counterpart in the reference (nor in any reference interface): an addition of this
+ * library for callers that are not allowed to touch the device allocator once they are
+ * running — a process whose device memory is owned by its own pool, a control loop that
+ * cannot take the device-wide stall of a cudaMalloc/cudaFree, a sandboxed plugin capped at
+ * the footprint it declared.  One Lloyd iteration on buffers the CALLER owns: assign every
+ * point of x (n x d float32, device) to its nearest of centroids_in (k x d float64, device;
+ * same distance and tie rules as km_assign's binary64 path), write the labels (in/out:
+ * previous labels or -1), the new centroids (cluster means; an empty cluster keeps its
+ * centroid; may alias centroids_in), the member counts and {changed, inertia} — all device
+ * pointers, enqueued on `stream` (a cudaStream_t, NULL = default stream) without waiting.
+ * The library's own working memory for this call is a fixed 256 KiB array built into the
+ * library image: it is held by every GPU that loads libkmeans.so until the process exits,
+ * it limits the shape to k*(2d+1)+4 <= 32768 (larger shapes fail with KM_ERR_UNSUPPORTED),
+ * and it is shared by every call on that GPU — the call clears what it needs first, and two
+ * calls whose GPU work overlaps would corrupt each other, so issue them one after another.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress);
+ * make that first call before any stream capture.  Calls no allocating routine. */
+typedef struct km_noalloc_result {
+  int64_t changed;  /* labels this call changed */
+  double inertia;   /* sum of winner distances */
+  int64_t n;
+  int32_t status;   /* KM_OK, or KM_ERR_NONFINITE if a point was NaN/Inf (outputs then undefined) */
+  int32_t pad;
+} km_noalloc_result;
+KM_API km_status km_lloyd_step_noalloc(int32_t device, void *stream, const float *x, int64_t n, int32_t d,
+                                       const double *centroids_in, int32_t k, int32_t *labels,
+                                       double *centroids_out, int64_t *counts_out, km_noalloc_result *result);
+
 KM_API km_status km_sync(km_ctx *ctx);
 /* with km_config.profile_kernels: summed device time of the assignment kernels launched
  * since the last reset (up to 256 are kept), and how many there were */

@@ -32,6 +32,11 @@ class Stats(C.Structure):
         return {f: getattr(self, f) for f, _ in self._fields_}
 
 
+class NoAllocResult(C.Structure):
+    _fields_ = [("changed", C.c_int64), ("inertia", C.c_double), ("n", C.c_int64), ("status", C.c_int32),
+                ("pad", C.c_int32)]
+
+
 # name -> (restype, argtypes); tests check this table against include/kmeans.h
 _vp, _i32, _i64, _u64, _dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_double
 PROTOTYPES = {
@@ -61,6 +66,7 @@ PROTOTYPES = {
     "km_get_counts": (_i32, [_vp, _vp]),
     "km_get_balance": (_i32, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_dbl)]),
     "km_get_sums": (_i32, [_vp, _vp, _vp, _vp]),
+    "km_lloyd_step_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "km_sync": (_i32, [_vp]),
     "km_kernel_time": (_i32, [_vp, C.POINTER(_dbl), C.POINTER(_i32), _i32]),
     "km_launch_count": (_i64, [_vp]),

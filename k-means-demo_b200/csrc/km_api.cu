@@ -18,6 +18,9 @@ static km_status fail(km_ctx *ctx, km_status code, const std::string &msg) {
   if (ctx) ctx->err = msg; else g_create_err = msg;
   return code;
 }
+// for the translation units that have no ctx to hang an error text on
+void km_internal_set_thread_error(const char *msg) { g_create_err = msg ? msg : ""; }
+
 #define KM_CUDA(ctx, expr)                                                                      \
   do {                                                                                          \
     cudaError_t _e = (expr);                                                                    \
