@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define KM_ABI_VERSION 1
+#define KM_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define KM_API __attribute__((visibility("default")))
@@ -76,6 +76,8 @@ typedef struct km_config {
                             0: from the filter's binary32 distances (<=1e-5 rel) */
   int32_t profile_kernels; /* 1: bracket each assignment kernel with CUDA events (km_kernel_time) */
   void *stream;        /* cudaStream_t to run on, or NULL for a private stream */
+  int32_t no_prune;    /* 1: never use the d = 2 candidate grid (brute force over all k) */
+  int32_t prune_min_points; /* 0: default threshold; else prune once a rank holds this many points */
 } km_config;
 
 typedef struct km_stats {

@@ -14,13 +14,13 @@ ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_OOM, ERR_STATE, ERR_NONFINITE, ERR_UNSU
 DTYPE_F32, DTYPE_F64 = 0, 1
 PATH_AUTO, PATH_DIRECT_F64, PATH_FILTER_F32, PATH_TENSOR = 0, 1, 2, 3
 UPDATE_INCREMENTAL, UPDATE_FULL = 0, 1
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class Config(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("device", C.c_int32), ("path", C.c_int32),
                 ("update_mode", C.c_int32), ("exact_inertia", C.c_int32), ("profile_kernels", C.c_int32),
-                ("stream", C.c_void_p)]
+                ("stream", C.c_void_p), ("no_prune", C.c_int32), ("prune_min_points", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -34,11 +34,12 @@ class KMeansState:
     """One km_ctx: one GPU's shard of the points, the centroids, labels and sums."""
 
     def __init__(self, device=0, path=L.PATH_AUTO, update_mode=L.UPDATE_INCREMENTAL, exact_inertia=True,
-                 stream=None, profile_kernels=False):
+                 stream=None, profile_kernels=False, no_prune=False, prune_min_points=0):
         self._lib = L.load()
         cfg = L.Config(struct_size=C.sizeof(L.Config), device=device, path=path, update_mode=update_mode,
                        exact_inertia=1 if exact_inertia else 0,
-                       profile_kernels=1 if profile_kernels else 0, stream=stream)
+                       profile_kernels=1 if profile_kernels else 0, stream=stream,
+                       no_prune=1 if no_prune else 0, prune_min_points=prune_min_points)
         h = C.c_void_p()
         st = self._lib.km_create(C.byref(cfg), C.byref(h))
         if st != L.OK:

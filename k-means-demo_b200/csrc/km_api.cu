@@ -238,20 +238,31 @@ static km_status adopt_points(km_ctx *ctx) {
                                  &ctx->launches);
   double hmax = 0.0;
   int hbad = 0;
+  unsigned hbox[4] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
+  const bool want_bbox = ctx->d == 2 && ctx->dtype == KM_DTYPE_F32 && (reinterpret_cast<uintptr_t>(ctx->x) & 7) == 0;
+  if (e == cudaSuccess && want_bbox) {
+    e = km_launch_bbox2((const float *)ctx->x, ctx->n, ctx->scan_bbox, ctx->sm_count, ctx->stream, &ctx->launches);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hbox, ctx->scan_bbox, sizeof(hbox), cudaMemcpyDeviceToHost, ctx->stream);
+  }
   if (e == cudaSuccess) e = cudaMemcpyAsync(&hmax, d_max, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(&hbad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   int64_t n_total = ctx->n, i0 = 0;
+  auto ord2f = [](unsigned u) { unsigned b = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u; float f; memcpy(&f, &b, 4); return (double)f; };
+  // this rank's box; an empty shard contributes an inverted (ignored) one
+  double box[4] = {INFINITY, -INFINITY, INFINITY, -INFINITY};
+  if (want_bbox && ctx->n > 0 && e == cudaSuccess) for (int q = 0; q < 4; q++) box[q] = ord2f(hbox[q]);
+  const int NG = 7;
   if (e == cudaSuccess && ctx->world > 1) {
-    // job-wide: max of max|x|, any non-finite, shard offsets — one all-gather of 3 doubles
+    // job-wide: max of max|x|, any non-finite, shard offsets, bounding box — one all-gather
     double *d_in = nullptr, *d_out = nullptr;
-    e = cudaMalloc(&d_in, 3 * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&d_out, 3 * sizeof(double) * ctx->world);
-    double h_in[3] = {hmax, (double)hbad, (double)ctx->n};
-    std::vector<double> h_out(3 * (size_t)ctx->world);
+    e = cudaMalloc(&d_in, NG * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, NG * sizeof(double) * ctx->world);
+    double h_in[NG] = {hmax, (double)hbad, (double)ctx->n, box[0], box[1], box[2], box[3]};
+    std::vector<double> h_out(NG * (size_t)ctx->world);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, ctx->stream);
     int r = 0;
-    if (e == cudaSuccess) r = g_nccl.all_gather(d_in, d_out, 3, KM_NCCL_FLOAT64, ctx->nccl_comm, ctx->stream);
+    if (e == cudaSuccess) r = g_nccl.all_gather(d_in, d_out, NG, KM_NCCL_FLOAT64, ctx->nccl_comm, ctx->stream);
     if (e == cudaSuccess && r == 0)
       e = cudaMemcpyAsync(h_out.data(), d_out, h_out.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess && r == 0) e = cudaStreamSynchronize(ctx->stream);
@@ -261,16 +272,20 @@ static km_status adopt_points(km_ctx *ctx) {
     if (e == cudaSuccess) {
       n_total = 0;
       for (int q = 0; q < ctx->world; q++) {
-        hmax = std::max(hmax, h_out[3 * q]);
-        hbad |= (h_out[3 * q + 1] != 0.0);
-        if (q < ctx->rank) i0 += (int64_t)h_out[3 * q + 2];
-        n_total += (int64_t)h_out[3 * q + 2];
+        hmax = std::max(hmax, h_out[NG * q]);
+        hbad |= (h_out[NG * q + 1] != 0.0);
+        if (q < ctx->rank) i0 += (int64_t)h_out[NG * q + 2];
+        n_total += (int64_t)h_out[NG * q + 2];
+        box[0] = std::min(box[0], h_out[NG * q + 3]); box[1] = std::max(box[1], h_out[NG * q + 4]);
+        box[2] = std::min(box[2], h_out[NG * q + 5]); box[3] = std::max(box[3], h_out[NG * q + 6]);
       }
     }
   }
   KM_CUDA(ctx, e);
   if (hbad) { free_points(ctx); return fail(ctx, KM_ERR_NONFINITE, "points contain NaN or Inf"); }
   ctx->maxabs = hmax;
+  ctx->have_bbox = want_bbox && box[0] <= box[1] && box[2] <= box[3];
+  for (int q = 0; q < 4; q++) ctx->bbox[q] = box[q];
   ctx->n_total = n_total;
   ctx->i0 = i0;
   ctx->have_points = true;
@@ -366,6 +381,7 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   KM_CREATE_CUDA(cudaMemset(ctx->state, 0, sizeof(KmState)));
   KM_CREATE_CUDA(cudaMalloc(&ctx->scan_max, sizeof(double)));
   KM_CREATE_CUDA(cudaMalloc(&ctx->scan_bad, sizeof(int)));
+  KM_CREATE_CUDA(cudaMalloc(&ctx->scan_bbox, 4 * sizeof(unsigned)));
   for (int q = 0; q < KM_PROF_RING; q++) {
     KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][0]));
     KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][1]));
@@ -391,6 +407,7 @@ extern "C" km_status km_destroy(km_ctx *ctx) {
   if (ctx->state) cudaFree(ctx->state);
   if (ctx->scan_max) cudaFree(ctx->scan_max);
   if (ctx->scan_bad) cudaFree(ctx->scan_bad);
+  if (ctx->scan_bbox) cudaFree(ctx->scan_bbox);
   for (int q = 0; q < KM_PROF_RING; q++)
     for (int w = 0; w < 2; w++) if (ctx->prof_ev[q][w]) cudaEventDestroy(ctx->prof_ev[q][w]);
   if (ctx->ring) cudaFreeHost(ctx->ring);
@@ -622,7 +639,6 @@ static km_status ready(km_ctx *ctx) {
   return KM_OK;
 }
 
-static int pick_path(km_ctx *ctx) { return pick_path_for(ctx, ctx->k); }
 
 static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.x = ctx->x; a.dtype = ctx->dtype; a.n = ctx->n; a.d = ctx->d; a.k = ctx->k;
@@ -635,6 +651,11 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.scale_a = ldexp(1.0, ctx->qa);
   a.scale_b = ldexp(1.0, ctx->QB);
   memset(&a.ps, 0, sizeof(a.ps));
+  memset(&a.pr, 0, sizeof(a.pr));
+  a.prune = 0;
+  if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
+      km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
+    a.prune = 1;
 }
 
 // ---- general path: assignment kernel, [NCCL all-reduce of the packed table], finalize kernel

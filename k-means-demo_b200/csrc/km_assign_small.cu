@@ -65,6 +65,9 @@ struct KmSmallCfg {
   static constexpr bool TAIL = (D & 1) != 0;                    // odd last dimension handled as a scalar
 };
 
+#define KM_PRUNE_MAGIC 12582912.0f
+#define KM_PRUNE_CAP 7   // candidates kept per cell (one 64-bit word: count byte + 7 indices)
+
 struct KmSmallParams {
   const float *x;
   int64_t n;
@@ -78,6 +81,7 @@ struct KmSmallParams {
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
   int64_t chunk;       // points per block (multiple of 4)
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
+  KmPrune2 pr;         // d == 2 candidate grid (used by the PRUNE instantiation)
 };
 
 // What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
@@ -147,8 +151,9 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
   }
 }
 
-template <int D, bool HILO>
+template <int D, bool HILO, bool PRUNE>
 __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
+  static_assert(!PRUNE || D == 2, "candidate pruning is built for d == 2");
   using Cfg = KmSmallCfg<D>;
   constexpr int PPV = Cfg::PPV, NV = Cfg::NV, PPT = Cfg::PPT, NP = Cfg::NP;
   constexpr bool TAIL = Cfg::TAIL;
@@ -160,6 +165,8 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   double *cd = reinterpret_cast<double *>(ncf + (((size_t)k * CROW + 3) & ~(size_t)3));  // [k][D] binary64 masters
   long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);               // optional per-block table
   const KmAccLayout L = km_acc_layout(k, D);
+  unsigned long long *cells =                                                         // PRUNE: candidate word per cell
+      reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal : 0));
   const KmPass &ps = p.ps;
 
   // this block's contiguous chunk of points, walked in rounds of THREADS*PPT; everything
@@ -209,7 +216,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   }
   __shared__ double s_red[2][KM_SMALL_THREADS / 32];
   __shared__ double s_iscale;
-  __shared__ float s_tau;
+  __shared__ float s_tau, s_cmaxf;
   __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, inertia limbs, rescored
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int red_warps = min(KM_SMALL_THREADS / 32, (k * D + 31) / 32);   // warps that saw an element
@@ -235,6 +242,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     const KmScales sc = km_scales_from_cmax(mn, ps.maxabs_x, D, ps.QB);
     s_iscale = sc.inertia_scale;
     s_tau = HILO ? sc.tau_hilo : sc.tau_hi;
+    s_cmaxf = __double2float_ru(mn);
     if (blockIdx.x == 0 && pend && ps.slot) {
       // the pending pass ran under the scales of C_in
       const KmScales si = km_scales_from_cmax(mi, ps.maxabs_x, D, ps.QB);
@@ -255,6 +263,38 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
 
+  if constexpr (PRUNE) {
+    // Candidate list of a cell with centre m and half diagonal r: every centroid within
+    // d_min + 2r of m.  For any x in the cell the nearest-to-m centroid is within d_min + r,
+    // and a centroid beyond d_min + 2r of m is farther than d_min + r from x — it can neither
+    // win nor tie.  r is inflated (0.1% + 1e-6 of the coordinate scale) to cover the
+    // binary32 arithmetic of this build; the point->cell map itself is exact.
+    const KmPrune2 &pr = p.pr;
+    const float r_eff = pr.r * 1.001f + 1e-6f * fmaxf(s_cmaxf, pr.absmax);
+    for (int cell = threadIdx.x; cell < pr.gp * pr.gp; cell += KM_SMALL_THREADS) {
+      const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
+      const float mx = ((float)ix - pr.kx) * pr.inv_sx, my = ((float)iy - pr.ky) * pr.inv_sy;
+      float dmin2 = __int_as_float(0x7f800000);
+      for (int j = 0; j < k; j++) {
+        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
+        dmin2 = fminf(dmin2, fmaf(dx, dx, dy * dy));
+      }
+      const float T = sqrtf(dmin2) + 2.0f * r_eff;
+      const float T2 = T * T * 1.00001f;
+      unsigned long long word = 0;
+      int cnt = 0;
+      for (int j = 0; j < k; j++) {
+        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
+        if (fmaf(dx, dx, dy * dy) <= T2) {
+          if (cnt < KM_PRUNE_CAP) word |= (unsigned long long)j << (8 * (cnt + 1));
+          cnt++;
+        }
+      }
+      cells[cell] = word | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
+    }
+    __syncthreads();
+  }
+
   int changed = 0, rescored = 0;
   double inertia = 0.0;
 
@@ -268,6 +308,44 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 #pragma unroll
     for (int q = 0; q < PPT; q++) { m1[q] = 0xFFFFFFFFu; m2[q] = 0xFFFFFFFFu; }
 
+    if constexpr (PRUNE) {
+      // each point looks only at its cell's candidates; a cell that overflowed its word
+      // (count byte 0xFF) sends its points to the binary64 scan of all k below
+      const KmPrune2 &pr = p.pr;
+      unsigned long long w[PPT];
+      int nn[PPT], nmax = 0;
+#pragma unroll
+      for (int q = 0; q < PPT; q++) {
+        float x0, x1;
+        unpk2(cur.xq[q][0], x0, x1);
+        // every real point maps inside the grid; the clamp is for the zero-filled lanes past
+        // the end of a ragged round (a negative index shows up as a huge masked value)
+        const int ix = min(__float_as_int(fmaf(x0, pr.sx, pr.kxm)) & 0x3FFFFF, pr.gp - 1);
+        const int iy = min(__float_as_int(fmaf(x1, pr.sy, pr.kym)) & 0x3FFFFF, pr.gp - 1);
+        w[q] = cells[iy * pr.gp + ix];
+        nn[q] = (int)(w[q] & 0xFF);
+        if (nn[q] == 0xFF) nn[q] = 0;   // overflow: leave m1 = m2 = max -> "ambiguous" -> full scan
+        nmax = max(nmax, nn[q]);
+      }
+#pragma unroll
+      for (int c = 0; c < KM_PRUNE_CAP; c++) {
+        if (c >= nmax) break;
+#pragma unroll
+        for (int q = 0; q < PPT; q++) {
+          if (c < nn[q]) {
+            const int j = (int)((w[q] >> (8 * (c + 1))) & 0xFF);
+            const float *crow = ncf + j * CROW;
+            f32x2 df = add2(cur.xq[q][0], *reinterpret_cast<const f32x2 *>(crow));
+            if (HILO) df = add2(df, *reinterpret_cast<const f32x2 *>(crow + 2));
+            float lo, hi;
+            unpk2(mul2(df, df), lo, hi);
+            const unsigned key = (__float_as_uint(lo + hi) & ~mask) | (unsigned)j;
+            m2[q] = min(m2[q], max(m1[q], key));
+            m1[q] = min(m1[q], key);
+          }
+        }
+      }
+    } else {
 #pragma unroll 4
     for (int j = 0; j < k; j++) {
       const float *crow = ncf + j * CROW;
@@ -315,6 +393,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         m1[q] = min(m1[q], key);
       }
     }
+    }
 
     // ---- per point: ambiguity test, rare binary64 re-score, inertia, commit.  A round that
     // lies wholly inside the chunk takes the copy with no bounds checks.
@@ -334,8 +413,10 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
         if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
         const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
-        // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score
-        const bool clear = (b2 - b1) > fmaf(rho2, b2, tau2);
+        // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score.
+        // No runner-up at all (k == 1, or a pruned cell with a single candidate) is unambiguous
+        // by construction; no winner at all (an overflowed cell) is not.
+        const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
         double best;
         if (!clear) {
           rescored++;
@@ -416,7 +497,7 @@ bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin
   return small_centroid_smem(d, k, true) + 4096 <= (size_t)max_smem_optin / 2;
 }
 
-template <int D, bool HILO>
+template <int D, bool HILO, bool PRUNE>
 static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   const KmAccLayout L = km_acc_layout(a.k, D);
   size_t smem = small_centroid_smem(D, a.k, HILO);
@@ -435,7 +516,11 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   p.key_mask = (1u << bits) - 1u;
   // (D+6) u for the arithmetic, 2^-(23-bits) for the key truncation, x2.5 margin
   p.rho2 = 2.5f * ((float)(D + 6) * 0x1.0p-24f + ldexpf(1.0f, bits - 23));
-  auto kern = km_assign_small_kernel<D, HILO>;
+  if (PRUNE) {
+    p.pr = a.pr;
+    smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);
+  }
+  auto kern = km_assign_small_kernel<D, HILO, PRUNE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -467,14 +552,14 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
 template <bool HILO>
 static cudaError_t dispatch_small(const KmAssignArgs &a, int64_t *launches) {
   switch (a.d) {
-    case 1: return launch_small<1, HILO>(a, launches);
-    case 2: return launch_small<2, HILO>(a, launches);
-    case 3: return launch_small<3, HILO>(a, launches);
-    case 4: return launch_small<4, HILO>(a, launches);
-    case 5: return launch_small<5, HILO>(a, launches);
-    case 6: return launch_small<6, HILO>(a, launches);
-    case 7: return launch_small<7, HILO>(a, launches);
-    case 8: return launch_small<8, HILO>(a, launches);
+    case 1: return launch_small<1, HILO, false>(a, launches);
+    case 2: return a.prune ? launch_small<2, HILO, true>(a, launches) : launch_small<2, HILO, false>(a, launches);
+    case 3: return launch_small<3, HILO, false>(a, launches);
+    case 4: return launch_small<4, HILO, false>(a, launches);
+    case 5: return launch_small<5, HILO, false>(a, launches);
+    case 6: return launch_small<6, HILO, false>(a, launches);
+    case 7: return launch_small<7, HILO, false>(a, launches);
+    case 8: return launch_small<8, HILO, false>(a, launches);
     default: return cudaErrorInvalidValue;
   }
 }
@@ -483,4 +568,34 @@ cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches) {
   if ((reinterpret_cast<uintptr_t>(a.x) & 15) || (reinterpret_cast<uintptr_t>(a.labels) & 15))
     return cudaErrorMisalignedAddress;
   return a.hilo ? dispatch_small<true>(a, launches) : dispatch_small<false>(a, launches);
+}
+
+// d == 2 candidate grid for this job's bounding box; false = do not prune this shape
+bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
+                          KmPrune2 *out) {
+  if (d != 2 || k < 16 || k > 256) return false;
+  // below ~32 points per thread the per-block grid build would not pay off
+  const int64_t need = min_points > 0 ? min_points : (int64_t)sm_count * 2 * KM_SMALL_THREADS * 32;
+  if (n_local < need) return false;
+  int g = 16;
+  while (g < 64 && g * g < 64 * k) g *= 2;   // ~8 cells across a Voronoi cell, capped by shared memory
+  const double wx = bbox[1] - bbox[0], wy = bbox[3] - bbox[2];
+  if (!(wx > 0.0) || !(wy > 0.0)) return false;
+  const double sx = g / (wx * (1.0 + 1e-6)), sy = g / (wy * (1.0 + 1e-6));
+  const double kx = ceil(0.5 - bbox[0] * sx) + 1.0, ky = ceil(0.5 - bbox[2] * sy) + 1.0;
+  if (fabs(kx) > 1e6 || fabs(ky) > 1e6) return false;   // box far from the origin relative to its size
+  out->gp = g + 4;
+  out->sx = (float)sx; out->sy = (float)sy;
+  out->kx = (float)kx; out->ky = (float)ky;
+  out->kxm = (float)kx + KM_PRUNE_MAGIC; out->kym = (float)ky + KM_PRUNE_MAGIC;
+  out->inv_sx = 1.0f / out->sx; out->inv_sy = 1.0f / out->sy;
+  out->r = 0.5f * sqrtf(out->inv_sx * out->inv_sx + out->inv_sy * out->inv_sy);
+  out->absmax = (float)fmax(fmax(fabs(bbox[0]), fabs(bbox[1])), fmax(fabs(bbox[2]), fabs(bbox[3])));
+  // every point must land inside [0, gp): check the corners with the kernel's own arithmetic
+  const float xs[2] = {(float)bbox[0], (float)bbox[1]}, ys[2] = {(float)bbox[2], (float)bbox[3]};
+  for (int q = 0; q < 2; q++) {
+    const float fx = fmaf(xs[q], out->sx, out->kx), fy = fmaf(ys[q], out->sy, out->ky);
+    if (!(fx >= 0.5f && fx < out->gp - 0.5f && fy >= 0.5f && fy < out->gp - 0.5f)) return false;
+  }
+  return true;
 }

@@ -72,6 +72,20 @@ struct KmPass {
   double maxabs_x;
 };
 
+// d == 2 candidate pruning.  A point's cell is RN(x*sx + Kx), RN(y*sy + Ky):
+// one FMA per axis against (K + 1.5*2^23), the integer then sits in the low mantissa bits —
+// and because the FMA rounds the exact value once, "x belongs to cell ix" means exactly
+// |x*sx + Kx - ix| <= 1/2: cells are exact boxes, no slack needed for the mapping.
+struct KmPrune2 {
+  int gp;              // cells per side (grid + margins)
+  float sx, sy;        // cells per unit length
+  float kxm, kym;      // K + 12582912.0f, both integers
+  float kx, ky;        // K
+  float inv_sx, inv_sy;
+  float r;             // half diagonal of a cell
+  float absmax;        // max |coordinate| of the bounding box
+};
+
 // One slot of the pinned-host stats ring the finalize kernel writes.
 struct KmStatSlot {
   long long it;

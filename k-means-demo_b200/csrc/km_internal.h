@@ -30,6 +30,8 @@ struct km_ctx {
   int64_t n_total = 0;
   int32_t d = 0;
   double maxabs = 0.0;        // over the whole job
+  double bbox[4] = {0, 0, 0, 0};  // d == 2, float32: job-wide xmin, xmax, ymin, ymax
+  bool have_bbox = false;
   bool have_points = false;
   int32_t *labels = nullptr;  // device, n
   void *pinned = nullptr;     // staging for uploads / downloads
@@ -60,6 +62,7 @@ struct km_ctx {
 
   double *scan_max = nullptr;       // device scratch of the upload scan
   int *scan_bad = nullptr;
+  unsigned *scan_bbox = nullptr;    // device, 4 ordered-uint encodings
   cudaEvent_t prof_ev[KM_PROF_RING][2];
   int prof_n = 0;
 
@@ -98,16 +101,21 @@ struct KmAssignArgs {
   double scale_a, scale_b;  // 2^qa, 2^QB (host copies of KmState's)
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
+  int prune;           // small-d path, d == 2: use the candidate grid `pr`
+  KmPrune2 pr;
   cudaStream_t stream;
 };
 
 // each returns cudaError_t and bumps *launches by the number of kernels enqueued
 cudaError_t km_launch_assign_direct(const KmAssignArgs &a, int64_t *launches);
 cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches);
+bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
+                          KmPrune2 *out);
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 
 cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxabs_out /*device*/,
                            int *nonfinite_out /*device*/, int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_bbox2(const float *x, int64_t n, unsigned *out4, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int32_t k_true, uint64_t seed,
                                 double sigma, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, cudaStream_t s, int64_t *launches);

@@ -44,6 +44,37 @@ cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxa
   return cudaGetLastError();
 }
 
+// bounding box of d == 2 float32 points (for the candidate grid): ordered-integer min/max
+__device__ __forceinline__ unsigned km_f2ord(float f) {
+  unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__global__ void __launch_bounds__(256) km_bbox2_kernel(const float2 *__restrict__ x, int64_t n, unsigned *out4) {
+  unsigned lox = 0xFFFFFFFFu, hix = 0u, loy = 0xFFFFFFFFu, hiy = 0u;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float2 v = x[i];
+    const unsigned a = km_f2ord(v.x), b = km_f2ord(v.y);
+    lox = min(lox, a); hix = max(hix, a); loy = min(loy, b); hiy = max(hiy, b);
+  }
+  lox = __reduce_min_sync(0xffffffffu, lox); hix = __reduce_max_sync(0xffffffffu, hix);
+  loy = __reduce_min_sync(0xffffffffu, loy); hiy = __reduce_max_sync(0xffffffffu, hiy);
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(out4 + 0, lox); atomicMax(out4 + 1, hix); atomicMin(out4 + 2, loy); atomicMax(out4 + 3, hiy);
+  }
+}
+
+// out4 (device, 4 unsigned): ordered encodings of xmin, xmax, ymin, ymax
+cudaError_t km_launch_bbox2(const float *x, int64_t n, unsigned *out4, int sm_count, cudaStream_t s, int64_t *launches) {
+  const unsigned init[4] = {0xFFFFFFFFu, 0u, 0xFFFFFFFFu, 0u};
+  cudaError_t e = cudaMemcpyAsync(out4, init, sizeof(init), cudaMemcpyHostToDevice, s);
+  if (e != cudaSuccess || n == 0) return e;
+  int64_t want = (n + 256 * 8 - 1) / (256 * 8);
+  int grid = (int)(want < (int64_t)sm_count * 8 ? want : (int64_t)sm_count * 8);
+  km_bbox2_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const float2 *>(x), n, out4);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ A8: generator
 __global__ void __launch_bounds__(256) km_gen_blobs_kernel(float *__restrict__ x, int64_t n, int64_t i0, int32_t d,
                                                            int32_t k_true, uint64_t seed, double sigma) {

@@ -43,7 +43,7 @@ def test_ctypes_table_matches_header(km):
     assert km._lib.load().km_abi_version() == km._lib.ABI_VERSION
     hdr = open(HEADER).read()
     assert f"#define KM_ABI_VERSION {km._lib.ABI_VERSION}" in hdr
-    assert C.sizeof(km._lib.Config) == 32 and C.sizeof(km._lib.Stats) == 48
+    assert C.sizeof(km._lib.Config) == 40 and C.sizeof(km._lib.Stats) == 48
 
 
 def test_struct_layout_agrees_with_compiler(tmp_path):
@@ -54,7 +54,7 @@ def test_struct_layout_agrees_with_compiler(tmp_path):
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
-    assert got == ["32", "48", "24", "16", "40"]
+    assert got == ["40", "48", "24", "16", "40"]
 
 
 def test_no_cpu_fallback_without_device(km):

@@ -366,3 +366,56 @@ def test_large_properties_d2_k64(km):
         xs = st.get_points(0, 200000)
         olab, _, _ = oracle.assign(xs, c_before)
         assert np.array_equal(lab, olab)
+
+
+# ---------------------------------------------------------------- d = 2 candidate-grid pruning
+def pruned_run(km, x, c0, max_iter=60, update_mode=0):
+    return gpu_run(km, x, c0, max_iter, "auto", update_mode, prune_min_points=1)
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["incremental", "full"])
+@pytest.mark.parametrize("shape", [(12000, 64, 64), (30000, 16, 16), (9000, 5, 200), (20000, 256, 256), (4000, 3, 40)],
+                         ids=lambda s: "n%d_kt%d_k%d" % s)
+def test_pruned_matches_oracle_and_brute_force(km, shape, mode):
+    n, k_true, k = shape
+    x = oracle.gen_blobs(300 + k, n, 2, k_true)
+    c0 = oracle.forgy_init(x, k, 5)
+    g = pruned_run(km, x, c0, 50, mode)
+    b = gpu_run(km, x, c0, 50, "auto", mode, no_prune=True)
+    o = oracle.run(x, c0, max_iter=50)
+    e = oracle.run(x, c0, max_iter=50, sum_mode=oracle.SUM_EXACT)
+    assert g["iterations"] == o["iterations"] == b["iterations"]
+    assert np.array_equal(g["labels"], o["labels"]) and np.array_equal(b["labels"], o["labels"])
+    assert np.array_equal(g["centroids"], e["centroids"]) and np.array_equal(b["centroids"], e["centroids"])
+    assert g["inertia"] == pytest.approx(o["inertia"], rel=REL)
+    assert g["rescored"] <= max(b["rescored"], 0) + n // 50  # overflowed cells add a few full scans, not many
+
+
+def test_pruned_adversarial_geometry(km):
+    rng = np.random.default_rng(12)
+    # duplicate centroids, a far outlier centroid, points on cell boundaries and exact lattice ties
+    xs = np.array([[x, y] for x in np.arange(-8, 8.25, 0.25) for y in np.arange(-8, 8.25, 0.25)], dtype=np.float32)
+    xs = np.concatenate([xs, (rng.standard_normal((5000, 2)) * 3).astype(np.float32)])
+    c0 = np.array([[x, y] for x in (-6, -2, 2, 6) for y in (-6, -2, 2, 6)] + [[2, 2], [500, 500], [-6, -6]], dtype=np.float64)
+    g = pruned_run(km, xs, c0, 30)
+    o = oracle.run(xs, c0, max_iter=30)
+    assert g["iterations"] == o["iterations"] and np.array_equal(g["labels"], o["labels"])
+    assert close(g["centroids"], o["centroids"]) and g["inertia"] == pytest.approx(o["inertia"], rel=REL)
+    # all k centroids on one spot: every cell overflows its 7-candidate word -> full scans, still exact
+    c_same = np.tile(np.array([[1.0, 1.0]]), (20, 1))
+    g = pruned_run(km, xs, c_same, 5)
+    o = oracle.run(xs, c_same, max_iter=5)
+    assert np.array_equal(g["labels"], o["labels"]) and g["iterations"] == o["iterations"]
+    # degenerate box (all x equal): pruning must switch itself off, not divide by zero
+    xl = np.stack([np.full(3000, 2.5, np.float32), rng.standard_normal(3000).astype(np.float32)], axis=1)
+    cl = oracle.forgy_init(xl, 16, 1)
+    g = pruned_run(km, xl, cl, 20)
+    o = oracle.run(xl, cl, max_iter=20)
+    assert np.array_equal(g["labels"], o["labels"]) and g["iterations"] == o["iterations"]
+    # data far from the origin relative to its spread
+    xf = (rng.standard_normal((20000, 2)) + np.array([4000.0, -9000.0])).astype(np.float32)
+    cf = oracle.forgy_init(xf, 32, 2)
+    g = pruned_run(km, xf, cf, 25)
+    o = oracle.run(xf, cf, max_iter=25)
+    assert np.array_equal(g["labels"], o["labels"]) and g["iterations"] == o["iterations"]
+    assert close(g["centroids"], o["centroids"])
