@@ -167,6 +167,12 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const KmAccLayout L = km_acc_layout(k, D);
   unsigned long long *cells =                                                         // PRUNE: candidate word per cell
       reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal : 0));
+  // per-warp queue of points whose sums must move (x, from, to): filled by ballot, drained 32
+  // at a time with every lane busy, instead of running the atomics under divergence
+  constexpr int QCAP = 64, QW = D + 2;
+  unsigned *qbuf = reinterpret_cast<unsigned *>(cells + (PRUNE ? p.pr.gp * p.pr.gp : 0)) +
+                   (threadIdx.x >> 5) * (QCAP * QW);
+  int q_head = 0, q_count = 0;   // warp-uniform
   const KmPass &ps = p.ps;
 
   // this block's contiguous chunk of points, walked in rounds of THREADS*PPT; everything
@@ -402,11 +408,8 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       int newlab[PPT];
 #pragma unroll
       for (int q = 0; q < PPT; q++) {
-        newlab[q] = cur.old[q];
-        if (!FULL) {
-          const int i = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV);
-          if (i >= cn) continue;
-        }
+        bool live = true;
+        if (!FULL) live = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV) < cn;
         int lab = (int)(m1[q] & mask);
         float xr[D];
 #pragma unroll
@@ -418,7 +421,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         // by construction; no winner at all (an overflowed cell) is not.
         const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
         double best;
-        if (!clear) {
+        if (live && !clear) {
           rescored++;
           best = __longlong_as_double(0x7FF0000000000000LL);
           lab = 0;
@@ -429,13 +432,35 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         } else {
           best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
         }
+        if (!live) { best = 0.0; lab = cur.old[q]; }
         inertia += best;
         newlab[q] = lab;
-        if (lab != cur.old[q]) {
-          changed++;
-          if (p.incremental) km_move_point(T, xr, D, lab, cur.old[q], scale_a, scale_b);
+        const bool moved = lab != cur.old[q];
+        changed += moved ? 1 : 0;
+        // queue the move (incremental: re-labelled points only; full: every live point)
+        const bool push = live && (p.incremental ? moved : true);
+        const unsigned bal = __ballot_sync(0xffffffffu, push);
+        if (bal) {
+          if (push) {
+            unsigned *e = qbuf + ((q_head + q_count + __popc(bal & ((1u << lane) - 1u))) & (QCAP - 1)) * QW;
+#pragma unroll
+            for (int t = 0; t < D; t++) e[t] = __float_as_uint(xr[t]);
+            e[D] = (unsigned)(p.incremental ? cur.old[q] : -1);
+            e[D + 1] = (unsigned)lab;
+          }
+          q_count += __popc(bal);
+          __syncwarp();
+          if (q_count >= 32) {
+            const unsigned *e = qbuf + ((q_head + lane) & (QCAP - 1)) * QW;
+            float xm[D];
+#pragma unroll
+            for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
+            km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
+            q_head = (q_head + 32) & (QCAP - 1);
+            q_count -= 32;
+            __syncwarp();
+          }
         }
-        if (!p.incremental) km_move_point(T, xr, D, lab, -1, scale_a, scale_b);
       }
 #pragma unroll
       for (int v = 0; v < NV; v++) {
@@ -462,6 +487,15 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     };
     if (r0 + per_round <= cn) tail(std::true_type{}); else tail(std::false_type{});
     cur = nxt;
+  }
+
+  // whatever is still queued (fewer than 32 entries per warp)
+  if (lane < q_count) {
+    const unsigned *e = qbuf + ((q_head + lane) & (QCAP - 1)) * QW;
+    float xm[D];
+#pragma unroll
+    for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
+    km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
   }
 
   // ---- block epilogue.  Counts go through one REDUX per warp; the inertia partial is summed
@@ -520,6 +554,7 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
     p.pr = a.pr;
     smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);
   }
+  smem += (size_t)(KM_SMALL_THREADS / 32) * 64 * (D + 2) * sizeof(unsigned);   // per-warp move queues
   auto kern = km_assign_small_kernel<D, HILO, PRUNE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
