@@ -270,28 +270,36 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const unsigned mask = p.key_mask;
 
   if constexpr (PRUNE) {
-    // Candidate list of a cell with centre m and half diagonal r: every centroid within
-    // d_min + 2r of m.  For any x in the cell the nearest-to-m centroid is within d_min + r,
-    // and a centroid beyond d_min + 2r of m is farther than d_min + r from x — it can neither
-    // win nor tie.  r is inflated (0.1% + 1e-6 of the coordinate scale) to cover the
-    // binary32 arithmetic of this build; the point->cell map itself is exact.
+    // Candidate list of a cell (a box with centre m and half sides hx/2, hy/2).  Let b be the
+    // centroid nearest to m.  For any other centroid j,
+    //     f_j(x) = |x - c_j|^2 - |x - c_b|^2 = a . x + const,   a = -2 (c_j - c_b)
+    // is LINEAR in x, so its minimum over the box is f_j(m) - (|a_x| hx + |a_y| hy) / 2.  If that
+    // minimum is positive, b beats j at every point of the box and j can neither win nor tie
+    // there: j is dropped.  Everything else (b included) is a candidate.  The test is exact
+    // geometry; `margin` (1e-5 of the squared coordinate scale, ~7x the binary32 error of
+    // the expressions below incl. the rounding of m) only ever keeps extra candidates.
     const KmPrune2 &pr = p.pr;
-    const float r_eff = pr.r * 1.001f + 1e-6f * fmaxf(s_cmaxf, pr.absmax);
+    const float M = s_cmaxf + pr.absmax;
+    const float margin = 1e-5f * M * M;
+    const float hx = pr.inv_sx, hy = pr.inv_sy;
     for (int cell = threadIdx.x; cell < pr.gp * pr.gp; cell += KM_SMALL_THREADS) {
       const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
       const float mx = ((float)ix - pr.kx) * pr.inv_sx, my = ((float)iy - pr.ky) * pr.inv_sy;
-      float dmin2 = __int_as_float(0x7f800000);
+      float dbest = __int_as_float(0x7f800000), bx = 0.f, by = 0.f;
       for (int j = 0; j < k; j++) {
-        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
-        dmin2 = fminf(dmin2, fmaf(dx, dx, dy * dy));
+        const float ncx = ncf[j * CROW], ncy = ncf[j * CROW + 1];   // negated centroid (hi part)
+        const float dx = mx + ncx, dy = my + ncy;
+        const float d2 = fmaf(dx, dx, dy * dy);
+        if (d2 < dbest) { dbest = d2; bx = ncx; by = ncy; }
       }
-      const float T = sqrtf(dmin2) + 2.0f * r_eff;
-      const float T2 = T * T * 1.00001f;
       unsigned long long word = 0;
       int cnt = 0;
       for (int j = 0; j < k; j++) {
-        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
-        if (fmaf(dx, dx, dy * dy) <= T2) {
+        const float ncx = ncf[j * CROW], ncy = ncf[j * CROW + 1];
+        const float dx = mx + ncx, dy = my + ncy;
+        const float fm = fmaf(dx, dx, dy * dy) - dbest;                                   // f_j(m)
+        const float swing = fabsf(ncx - bx) * hx + fabsf(ncy - by) * hy;                  // (|a_x| hx + |a_y| hy) / 2
+        if (fm - swing <= margin) {
           if (cnt < KM_PRUNE_CAP) word |= (unsigned long long)j << (8 * (cnt + 1));
           cnt++;
         }
