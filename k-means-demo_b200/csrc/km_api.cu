@@ -94,6 +94,8 @@ static km_status bind(km_ctx *ctx) {
 static void free_points(km_ctx *ctx) {
   if (ctx->x && ctx->own_x) cudaFree(ctx->x);
   if (ctx->labels) cudaFree(ctx->labels);
+  if (ctx->t_cand) cudaFree(ctx->t_cand);
+  ctx->t_cand = nullptr; ctx->t_cand_n = 0;
   ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
   ctx->n = 0; ctx->n_total = 0; ctx->i0 = 0;
 }
@@ -106,6 +108,8 @@ static void free_centroids(km_ctx *ctx) {
   ctx->c64 = nullptr; ctx->chi = ctx->clo = nullptr; ctx->acc = ctx->acc_global = nullptr;
   for (int q = 0; q < 2; q++) { if (ctx->p1S[q]) cudaFree(ctx->p1S[q]); if (ctx->p1C[q]) cudaFree(ctx->p1C[q]); ctx->p1S[q] = nullptr; ctx->p1C[q] = nullptr; }
   for (int q = 0; q < 3; q++) { if (ctx->p1D[q]) cudaFree(ctx->p1D[q]); ctx->p1D[q] = nullptr; }
+  if (ctx->t_cn) cudaFree(ctx->t_cn);
+  ctx->t_cn = nullptr;
   ctx->p1 = false; ctx->p1_pending = false;
   ctx->have_centroids = false; ctx->k = 0; ctx->acc_len = 0;
 }
@@ -513,7 +517,8 @@ extern "C" km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t 
 static int pick_path_for(km_ctx *ctx, int32_t k) {
   int want = ctx->cfg.path;
   bool small_ok = km_small_path_supported(ctx->d, k, ctx->dtype, ctx->max_smem_optin);
-  if (want == KM_PATH_AUTO) return small_ok ? KM_PATH_FILTER_F32 : KM_PATH_DIRECT_F64;
+  bool tensor_ok = km_tensor_path_supported(ctx->d, k, ctx->dtype, ctx->max_smem_optin);
+  if (want == KM_PATH_AUTO) return small_ok ? KM_PATH_FILTER_F32 : (tensor_ok && k >= 16) ? KM_PATH_TENSOR : KM_PATH_DIRECT_F64;
   return want;
 }
 
@@ -525,10 +530,12 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
   const int path = pick_path_for(ctx, k);
   if (path == KM_PATH_FILTER_F32 && !km_small_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
     return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096, k*d <= 8192");
-  if (path == KM_PATH_TENSOR) return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR is not built yet");
+  if (path == KM_PATH_TENSOR && !km_tensor_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
+    return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR needs float32 points, d a multiple of 32 up to 128, k >= 2");
   const bool p1 = path == KM_PATH_FILTER_F32;
-  if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len || ctx->p1 != p1) {
+  if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len || ctx->p1 != p1 || ctx->path_now != path) {
     free_centroids(ctx);
+    ctx->path_now = path;
     size_t kd = (size_t)k * d;
     if (p1) {
       for (int q = 0; q < 2; q++) {
@@ -545,6 +552,7 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
       KM_CUDA(ctx, cudaMalloc(&ctx->acc, (size_t)L.len * sizeof(long long)));
       if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
       else ctx->acc_global = ctx->acc;
+      if (path == KM_PATH_TENSOR) KM_CUDA(ctx, cudaMalloc(&ctx->t_cn, ((size_t)k + 512) * sizeof(float)));
     }
     ctx->k = k;
     ctx->acc_len = L.len;
@@ -652,6 +660,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.scale_b = ldexp(1.0, ctx->QB);
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
+  a.t_cn = nullptr; a.t_cand = nullptr; a.t_xnmax = 0.f;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
@@ -672,8 +681,21 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
   }
   const bool prof = ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
   if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
-  KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
-  ctx->last_path = KM_PATH_DIRECT_F64;
+  if (ctx->path_now == KM_PATH_TENSOR) {
+    if (ctx->t_cand_n < ctx->n) {
+      if (ctx->t_cand) cudaFree(ctx->t_cand);
+      ctx->t_cand = nullptr;
+      KM_CUDA(ctx, cudaMalloc(&ctx->t_cand, std::max<size_t>((size_t)ctx->n * KT_CAND * sizeof(int), 16)));
+      ctx->t_cand_n = ctx->n;
+    }
+    a.t_cn = ctx->t_cn; a.t_cand = ctx->t_cand;
+    a.t_xnmax = (float)(sqrt((double)ctx->d) * ctx->maxabs * (1.0 + 1e-6));
+    KM_CUDA(ctx, km_launch_assign_tensor(a, &ctx->launches));
+    ctx->last_path = KM_PATH_TENSOR;
+  } else {
+    KM_CUDA(ctx, km_launch_assign_direct(a, &ctx->launches));
+    ctx->last_path = KM_PATH_DIRECT_F64;
+  }
   if (prof) {
     KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][1], ctx->stream));
     ctx->prof_n++;

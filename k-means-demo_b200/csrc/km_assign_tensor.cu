@@ -1,0 +1,420 @@
+// km_assign_tensor.cu — KM_PATH_TENSOR: GEMM-form assignment on the 5th-gen tensor cores
+// (tcgen05.mma, accumulators in TMEM) for large k*d (BASELINE.json configs[2], configs[3]).
+//
+// Two stages:
+//
+//  1. COARSE, tensor cores.  For a tile of 128 points the kernel forms
+//         dist~(i,j) = |c_j|^2 - 2 x_i.c_j            (|x_i|^2 is the same for every j)
+//     with x.c from `tcgen05.mma.kind::tf32` (operands straight from the float32 rows, staged
+//     in shared memory in the canonical K-major 128-byte-swizzled layout; 128x128 fp32
+//     accumulator tiles double-buffered in TMEM so the MMA of centroid tile t+1 runs under
+//     the epilogue of tile t).  The N x k distance matrix never leaves the SM: the epilogue
+//     (tcgen05.ld, one TMEM lane = one point per thread) keeps, per point, only the
+//     centroids whose coarse distance is within 2E of the running minimum, where E is a
+//     rigorous bound on the TF32 error.  Any centroid outside that set is provably not the
+//     binary64 argmin.  At most KT_CAND survivors per point are written out (4 ints).
+//
+//  2. EXACT, CUDA cores (km_tensor_stage2_kernel, one warp per point).  The survivors —
+//     almost always 1 to 3 — are re-evaluated with direct binary32 differences and the same
+//     error-bound test as the small-d path, falling back to binary64 in the oracle's exact
+//     operation order when the gap is inside the bound.  Label compare, order-free sums
+//     (global int64 atomics), change count and inertia follow.
+//
+// So the labels are the oracle's bit for bit, and the tensor cores do all O(N k d) work.
+#include "km_commit.cuh"
+#include "km_internal.h"
+
+#define KT_M 128         // points per tile (UMMA M, cta_group::1)
+#define KT_N 128         // centroids per MMA tile (UMMA N)
+#define KT_THREADS 128   // 4 warps: warp w owns TMEM lanes [32w, 32w+32)
+#define KT_LIST 8        // per-point survivor list kept in shared memory while the tiles stream by
+#define KT_KBLK 32       // floats per 128-byte swizzled row
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// make generic-proxy writes to shared memory visible to the tensor core (async proxy)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot_in_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_in_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, FP32 accumulate; issued by ONE thread
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once every MMA issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: rows of 128 bytes, 8-row (1024 B) swizzle
+// atoms stacked along M/N (stride byte offset 1024), version 1 (Blackwell).  Fields as in
+// cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version [46,48),
+// layout type [61,64) with SWIZZLE_128B = 2.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 at [4,6), a/b format
+// TF32 = 2 at [7,10)/[10,13), both K-major, N>>3 at [17,23), M>>4 at [24,29).
+__device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// rare: the survivor list of a point is full -> drop what the tighter threshold has since excluded
+__device__ __noinline__ int kt_compact(int2 *lst, int row, float thr) {
+  int w = 0;
+  for (int s = 0; s < KT_LIST; s++) {
+    const int2 e = lst[s * KT_M + row];
+    if (__int_as_float(e.y) <= thr) lst[(w++) * KT_M + row] = e;
+  }
+  return w;
+}
+
+// ------------------------------------------------------------------ stage 1: coarse kernel
+struct KmTensorParams {
+  const float *x;      // [n][d]
+  int64_t n;
+  int d, k;
+  const float *chi;    // [k][d] binary32 centroids
+  const float *cn;     // [kpad] |chi_j|^2, +inf beyond k
+  const KmState *st;   // st->cnmax2 = max_j |chi_j|^2
+  float xnmax;         // upper bound of |x_i| over the job
+  int *cand;           // [n][KT_CAND]: survivors (ascending index), -1 = unused; cand[i][0] = -2: scan all k
+};
+
+// Copy `rows` x d floats (row stride d) into the swizzled K-major layout the UMMA descriptor
+// describes: k-block kb (32 floats) of row r lives at kb*(R*128) + r*128 + ((chunk ^ (r & 7)) * 16).
+// Rows at or beyond `valid` are zero-filled (cp.async with src-size 0).
+__device__ __forceinline__ void load_tile_sw128(uint32_t smem_base, const float *g, int64_t row0, int64_t valid_rows,
+                                                int d) {
+  const int chunks_per_row = d >> 2;
+  const int total = KT_M * chunks_per_row;
+  for (int c = threadIdx.x; c < total; c += KT_THREADS) {
+    const int r = c / chunks_per_row, q = c - r * chunks_per_row;
+    const int kb = q >> 3, ch = q & 7;
+    const uint32_t dst = smem_base + kb * (KT_M * 128) + r * 128 + ((ch ^ (r & 7)) << 4);
+    const bool ok = row0 + r < valid_rows;
+    const float *src = g + (ok ? (row0 + r) * (int64_t)d + q * 4 : 0);
+    cp_async16(dst, src, ok ? 16 : 0);
+  }
+}
+
+__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const KmTensorParams p) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const int d = p.d, kblocks = d / KT_KBLK;
+  const uint32_t tile_bytes = (uint32_t)KT_M * d * 4;            // one operand tile
+  unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const uint32_t sA = smem_u32(base), sB0 = sA + tile_bytes, sB1 = sB0 + tile_bytes;
+  unsigned char *tail = base + 3 * (size_t)tile_bytes;
+  float *cnb = reinterpret_cast<float *>(tail);                                  // [2][KT_N] centroid norms of the tile
+  int2 *lst = reinterpret_cast<int2 *>(tail + 2 * KT_N * sizeof(float));         // [KT_LIST][KT_M] (index, dist bits)
+  uint64_t *bars = reinterpret_cast<uint64_t *>(lst + KT_LIST * KT_M);           // [2] MMA-done barriers
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, row = threadIdx.x;
+  if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+  if (warp == 0) tmem_alloc(tmem_slot, 2 * KT_N);     // two 128-column fp32 accumulator tiles
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t idesc = umma_idesc_tf32(KT_M, KT_N);
+  const int ntiles = (p.k + KT_N - 1) / KT_N;
+  // rigorous TF32 bound: |dist~ - dist| <= E = 2^-7.5 |x_i| max_j|c_j| (+ fp32 slop)
+  const float cnmax = sqrtf(p.st->cnmax2);
+  const float two_e = 2.0f * (0.0055243f * p.xnmax * cnmax) + 1e-6f * (p.xnmax * p.xnmax + p.st->cnmax2);
+  uint32_t phase[2] = {0, 0};
+
+  const int64_t mtiles = (p.n + KT_M - 1) / KT_M;
+  for (int64_t mt = blockIdx.x; mt < mtiles; mt += gridDim.x) {
+    const int64_t row0 = mt * KT_M;
+    // ---- A tile and the first B tile
+    load_tile_sw128(sA, p.x, row0, p.n, d);
+    load_tile_sw128(sB0, p.chi, 0, p.k, d);
+    if (threadIdx.x < KT_N) cnb[threadIdx.x] = p.cn[threadIdx.x];
+    cp_async_commit();
+    cp_async_wait<0>();
+    fence_proxy_async();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tc_fence_after();
+      for (int kb = 0; kb < kblocks; kb++)
+        for (int ks = 0; ks < 4; ks++)
+          umma_tf32(tmem_base, umma_desc_sw128(sA + kb * (KT_M * 128) + ks * 32),
+                    umma_desc_sw128(sB0 + kb * (KT_N * 128) + ks * 32), idesc, (kb | ks) != 0);
+      umma_commit(&bars[0]);
+    }
+    if (ntiles > 1) {
+      load_tile_sw128(sB1, p.chi, KT_N, p.k, d);
+      if (threadIdx.x < KT_N) cnb[KT_N + threadIdx.x] = p.cn[KT_N + threadIdx.x];
+      cp_async_commit();
+    }
+    float runmin = __int_as_float(0x7f800000), thr = runmin;
+    int cnt = 0, overflow = 0;
+
+    for (int t = 0; t < ntiles; t++) {
+      const int b = t & 1;
+      if (t + 1 < ntiles) {
+        // B(t+1) has landed -> issue MMA(t+1) into the other TMEM buffer; it runs under epilogue(t)
+        cp_async_wait<0>();
+        fence_proxy_async();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          tc_fence_after();
+          const uint32_t sB = b ? sB0 : sB1;
+          for (int kb = 0; kb < kblocks; kb++)
+            for (int ks = 0; ks < 4; ks++)
+              umma_tf32(tmem_base + (uint32_t)((b ^ 1) * KT_N), umma_desc_sw128(sA + kb * (KT_M * 128) + ks * 32),
+                        umma_desc_sw128(sB + kb * (KT_N * 128) + ks * 32), idesc, (kb | ks) != 0);
+          umma_commit(&bars[b ^ 1]);
+        }
+      }
+      mbar_wait(&bars[b], phase[b]);     // MMA(t) done: TMEM buffer b is readable, B smem buffer b is free
+      phase[b] ^= 1;
+      tc_fence_after();
+      // epilogue(t): this thread's point against the 128 centroids of tile t
+      const float *cnt_tile = cnb + b * KT_N;
+#pragma unroll 1
+      for (int c = 0; c < KT_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * KT_N + c), v);
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+          const float dist = fmaf(-2.0f, __uint_as_float(v[i]), cnt_tile[c + i]);
+          if (dist <= thr) {
+            if (cnt == KT_LIST) cnt = kt_compact(lst, row, thr);
+            if (cnt < KT_LIST) lst[(cnt++) * KT_M + row] = make_int2(t * KT_N + c + i, __float_as_int(dist));
+            else overflow = 1;
+            if (dist < runmin) { runmin = dist; thr = runmin + two_e; }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncthreads();                   // every warp is done with TMEM buffer b and with cnb[b]
+      if (t + 2 < ntiles) {
+        load_tile_sw128(b ? sB1 : sB0, p.chi, (int64_t)(t + 2) * KT_N, p.k, d);
+        if (threadIdx.x < KT_N) cnb[b * KT_N + threadIdx.x] = p.cn[(t + 2) * KT_N + threadIdx.x];
+        cp_async_commit();
+      }
+    }
+    // ---- survivors of this point: within 2E of the final minimum, ascending index
+    if (row0 + row < p.n) {
+      int out[KT_CAND];
+      int w = 0;
+      for (int s = 0; s < cnt; s++) {
+        const int2 e = lst[s * KT_M + row];
+        if (__int_as_float(e.y) <= thr) {
+          if (w < KT_CAND) out[w] = e.x;
+          w++;
+        }
+      }
+      if (overflow || w > KT_CAND || w == 0) {
+        out[0] = -2;                       // too many to list: stage 2 scans all k
+        for (int s = 1; s < KT_CAND; s++) out[s] = -1;
+      } else {
+        for (int s = w; s < KT_CAND; s++) out[s] = -1;
+        for (int a = 1; a < w; a++)        // insertion sort, ascending index (tie rule: lowest j first)
+          for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
+      }
+      *reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND) = make_int4(out[0], out[1], out[2], out[3]);
+    }
+    __syncthreads();                       // lst and the operand buffers are reused by the next point tile
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 2 * KT_N);
+}
+
+// |chi_j|^2 per centroid (padded with +inf to a whole number of MMA tiles) and its maximum
+__global__ void __launch_bounds__(256) km_tensor_cnorm_kernel(const float *__restrict__ chi, int k, int d, int kpad,
+                                                              float *__restrict__ cn, KmState *st) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= kpad) return;
+  float s = 0.f;
+  if (warp < k)
+    for (int t = lane; t < d; t += 32) { const float v = chi[(int64_t)warp * d + t]; s = fmaf(v, v, s); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) {
+    cn[warp] = warp < k ? s : __int_as_float(0x7f800000);
+    if (warp < k) atomicMax(reinterpret_cast<unsigned int *>(&st->cnmax2), __float_as_uint(s));   // s >= 0: bits order = value order
+  }
+}
+
+// ------------------------------------------------------------------ stage 2: exact kernel
+// One warp per point; lanes split the dimensions.  Survivors are re-evaluated with direct
+// binary32 differences; the binary64 re-score (oracle operation order, one lane, sequential)
+// settles what the error bound cannot.
+__global__ void __launch_bounds__(256)
+km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, const int *__restrict__ cand,
+                        const float *__restrict__ chi, const double *__restrict__ c64, int32_t *__restrict__ labels,
+                        long long *__restrict__ acc, const KmState *__restrict__ st, int incremental, int exact_inertia) {
+  const KmAccLayout L = km_acc_layout(k, d);
+  const double scale_a = st->scale_a, scale_b = st->scale_b, inertia_scale = st->inertia_scale;
+  const float tau2 = st->tau_hi;
+  const float rho2 = 2.5f * (float)(d + 6) * 0x1.0p-24f;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  KmThreadScalars S;
+  double inertia = 0.0;
+  for (int64_t i = warp0; i < n; i += nwarps) {
+    const float *xr = x + i * (int64_t)d;
+    const int4 cw = *reinterpret_cast<const int4 *>(cand + i * KT_CAND);
+    const int cl[KT_CAND] = {cw.x, cw.y, cw.z, cw.w};
+    const bool scan_all = cl[0] == -2;
+    const int ncand = scan_all ? k : ((cl[1] < 0) ? 1 : (cl[2] < 0) ? 2 : (cl[3] < 0) ? 3 : 4);
+    float b1 = __int_as_float(0x7f800000), b2 = b1;
+    int i1 = scan_all ? 0 : cl[0];
+    if (ncand > 1) {
+      for (int s = 0; s < ncand; s++) {
+        const int j = scan_all ? s : cl[s];
+        const float *cr = chi + (int64_t)j * d;
+        float part = 0.f;
+        for (int t = lane; t < d; t += 32) { const float df = xr[t] - cr[t]; part = fmaf(df, df, part); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        if (part < b1) { b2 = b1; b1 = part; i1 = j; } else if (part < b2) b2 = part;
+      }
+    }
+    int lab = i1;
+    // a lone survivor is the argmin by the coarse bound; otherwise the binary32 gap must clear its own bound
+    const bool clear = ncand == 1 || (b2 - b1) > fmaf(rho2, b2, tau2);
+    double best = 0.0;
+    if (!clear) {
+      // binary64, dims ascending, separate multiply and add: the oracle's own arithmetic (A1/A2)
+      if (lane == 0) {
+        best = __longlong_as_double(0x7FF0000000000000LL);
+        lab = 0;
+        for (int s = 0; s < ncand; s++) {
+          const int j = scan_all ? s : cl[s];
+          const double dj = km_dist2_f64(xr, c64 + (int64_t)j * d, d);
+          if (dj < best) { best = dj; lab = j; }
+        }
+        S.rescored++;
+      }
+      lab = __shfl_sync(0xffffffffu, lab, 0);
+    } else if (exact_inertia) {
+      const double *cr = c64 + (int64_t)lab * d;
+      double part = 0.0;
+      for (int t = lane; t < d; t += 32) { const double df = __dsub_rn((double)xr[t], cr[t]); part = __dadd_rn(part, __dmul_rn(df, df)); }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      best = part;
+    } else {
+      best = (double)b1;
+      if (ncand == 1) {   // no binary32 distance was needed for the decision: take it now
+        const float *cr = chi + (int64_t)lab * d;
+        float part = 0.f;
+        for (int t = lane; t < d; t += 32) { const float df = xr[t] - cr[t]; part = fmaf(df, df, part); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        best = (double)part;
+      }
+    }
+    const int old = labels[i];
+    if (lane == 0) {
+      inertia += best;
+      if (lab != old) { S.changed++; labels[i] = lab; }
+    }
+    const bool move = incremental ? (lab != old) : true;
+    if (move) {
+      const int from = incremental ? old : -1;
+      for (int t = lane; t < d; t += 32) {
+        long long a, b;
+        km_fixed_split((double)xr[t], scale_a, scale_b, a, b);
+        km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
+        km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
+        if (from >= 0) {
+          km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
+          km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
+        }
+      }
+      if (lane == 0) {
+        km_atomic_add_ll(acc + L.cnt + lab, 1);
+        if (from >= 0) km_atomic_add_ll(acc + L.cnt + from, -1);
+      }
+    }
+  }
+  km_fixed_split(inertia, inertia_scale, scale_b, S.ia, S.ib);
+  km_flush_scalars(S, acc, L);
+}
+
+// ------------------------------------------------------------------ launcher
+bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin) {
+  if (dtype != KM_DTYPE_F32 || d % KT_KBLK != 0 || d < KT_KBLK || d > 128 || k < 2) return false;
+  const size_t smem = 3 * (size_t)KT_M * d * 4 + 2 * KT_N * 4 + (size_t)KT_LIST * KT_M * 8 + 64 + 1024;
+  return smem <= (size_t)max_smem_optin;
+}
+
+cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
+  const int kpad = ((a.k + KT_N - 1) / KT_N + 2) * KT_N;   // whole tiles, plus slack for the prefetch of cn
+  cudaError_t e = cudaMemsetAsync(&a.state->cnmax2, 0, sizeof(float), a.stream);
+  if (e != cudaSuccess) return e;
+  km_tensor_cnorm_kernel<<<(kpad * 32 + 255) / 256, 256, 0, a.stream>>>(a.chi, a.k, a.d, kpad, a.t_cn, a.state);
+  (*launches)++;
+  if (a.n > 0) {
+    KmTensorParams p;
+    p.x = (const float *)a.x; p.n = a.n; p.d = a.d; p.k = a.k; p.chi = a.chi; p.cn = a.t_cn; p.st = a.state;
+    p.xnmax = a.t_xnmax; p.cand = a.t_cand;
+    const size_t smem = 3 * (size_t)KT_M * a.d * 4 + 2 * KT_N * 4 + (size_t)KT_LIST * KT_M * 8 + 64 + 1024;
+    e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int64_t mtiles = (a.n + KT_M - 1) / KT_M;
+    const int grid = (int)(mtiles < a.sm_count ? mtiles : a.sm_count);
+    km_tensor_coarse_kernel<<<grid, KT_THREADS, smem, a.stream>>>(p);
+    (*launches)++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int64_t want = (a.n * 32 + 255) / 256;
+    const int64_t cap = (int64_t)a.sm_count * 8;
+    km_tensor_stage2_kernel<<<(int)(want < cap ? want : cap), 256, 0, a.stream>>>(
+        (const float *)a.x, a.n, a.d, a.k, a.t_cand, a.chi, a.c64, a.labels, a.acc, a.state, a.incremental, a.exact_inertia);
+    (*launches)++;
+  }
+  return cudaGetLastError();
+}

@@ -49,6 +49,8 @@ struct KmState {
   unsigned int ticket;   // last-block election in the finalize kernel
   int32_t it;            // assign steps since the last label reset
   unsigned long long cmax_bits;  // scratch for the finalize kernel's max reduction
+  float cnmax2;          // tensor path: max_j |chi_j|^2 of the current centroids
+  float pad0;
 };
 
 // Small-d path ("prologue-finalize" protocol): what one pass reads and writes.

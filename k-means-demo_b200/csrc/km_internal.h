@@ -10,6 +10,7 @@
 
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
+#define KT_CAND 4      // tensor path: survivors listed per point
 #define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
 
 struct km_ctx {
@@ -78,6 +79,12 @@ struct km_ctx {
   int p1_pend_update = 0, p1_pend_nc = 0;  // ... to be applied with this intent
   int32_t p1_pend_it = 0;
 
+  // ---- tensor path scratch
+  float *t_cn = nullptr;
+  int *t_cand = nullptr;
+  int64_t t_cand_n = 0;
+  int path_now = 0;                 // KM_PATH_* chosen for the current (points, centroids)
+
   // ---- multi-GPU
   int rank = 0, world = 1;
   void *nccl_comm = nullptr;
@@ -101,6 +108,9 @@ struct KmAssignArgs {
   double scale_a, scale_b;  // 2^qa, 2^QB (host copies of KmState's)
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
+  float *t_cn;         // tensor path: |chi_j|^2 (padded)
+  int *t_cand;         // tensor path: [n][KT_CAND] survivors of the coarse stage
+  float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
   KmPrune2 pr;
   cudaStream_t stream;
@@ -109,6 +119,8 @@ struct KmAssignArgs {
 // each returns cudaError_t and bumps *launches by the number of kernels enqueued
 cudaError_t km_launch_assign_direct(const KmAssignArgs &a, int64_t *launches);
 cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches);
+cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches);
+bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           KmPrune2 *out);
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);

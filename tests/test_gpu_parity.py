@@ -419,3 +419,53 @@ def test_pruned_adversarial_geometry(km):
     o = oracle.run(xf, cf, max_iter=25)
     assert np.array_equal(g["labels"], o["labels"]) and g["iterations"] == o["iterations"]
     assert close(g["centroids"], o["centroids"])
+
+
+# ---------------------------------------------------------------- tensor path (tcgen05 coarse stage + exact stage)
+@pytest.mark.parametrize("mode", [0, 1], ids=["incremental", "full"])
+@pytest.mark.parametrize("shape", [(3000, 32, 16, 16), (1500, 128, 8, 32), (20000, 64, 40, 200), (4099, 32, 3, 129),
+                                   (9000, 96, 500, 1024), (257, 128, 2, 2)],
+                         ids=lambda s: "n%d_d%d_kt%d_k%d" % s)
+def test_tensor_path_matches_oracle(km, shape, mode):
+    n, d, k_true, k = shape
+    x = oracle.gen_blobs(700 + d, n, d, k_true)
+    c0 = oracle.forgy_init(x, k, 9)
+    with km.KMeansState(path=km._lib.PATH_TENSOR, update_mode=mode) as st:
+        st.upload_points(x)
+        st.set_centroids(c0)
+        s = st.run(25)
+        assert s["path_used"] == km._lib.PATH_TENSOR
+        lab, cen, counts = st.labels(), st.centroids(), st.counts()
+    o = oracle.run(x, c0, max_iter=25, nthreads=0)
+    e = oracle.run(x, c0, max_iter=25, sum_mode=oracle.SUM_EXACT, nthreads=0)
+    assert s["iterations"] == o["iterations"] and np.array_equal(lab, o["labels"])
+    assert np.array_equal(cen, e["centroids"]) and close(cen, o["centroids"])
+    assert np.array_equal(counts, o["counts"])
+    assert s["inertia"] == pytest.approx(o["inertia"], rel=REL)
+
+
+def test_tensor_path_near_ties_and_duplicates(km):
+    # many centroids per blob (k >> k_true) makes within-blob near-ties the common case, the
+    # regime where the TF32 stage cannot decide and the exact stage must; plus exact duplicates
+    rng = np.random.default_rng(3)
+    x = oracle.gen_blobs(91, 6000, 64, 4)
+    c0 = oracle.forgy_init(x, 96, 4)
+    c0[50] = c0[7]                                  # duplicate centroid: index 7 must win every tie
+    x[100] = ((c0[3] + c0[11]) / 2).astype(np.float32)   # a point (almost) on a bisector
+    with km.KMeansState(path=km._lib.PATH_TENSOR) as st:
+        st.upload_points(x)
+        st.set_centroids(c0)
+        s = st.assign()
+        lab, _, inertia = oracle.assign(x, c0)
+        assert np.array_equal(st.labels(), lab) and not np.any(st.labels() == 50)
+        assert s["inertia"] == pytest.approx(inertia, rel=REL)
+    check_against_oracle(km, x, c0, max_iter=20, path="auto")
+
+
+def test_tensor_path_rejects_unsupported_shapes(km):
+    x = oracle.gen_blobs(1, 500, 48, 3)   # d not a multiple of 32
+    with km.KMeansState(path=km._lib.PATH_TENSOR) as st:
+        st.upload_points(x)
+        with pytest.raises(km.KMeansError) as e:
+            st.set_centroids(x[:4].astype(np.float64))
+        assert e.value.status == km._lib.ERR_UNSUPPORTED
