@@ -144,19 +144,28 @@ __device__ __forceinline__ void load_tile_sw128(uint32_t smem_base, const float 
   }
 }
 
-__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const KmTensorParams p) {
+// shared-memory bytes of the coarse kernel for dimension d
+static __host__ __device__ inline size_t kt_smem_bytes(int d) {
+  return 3 * (size_t)KT_M * d * 4          // A tile + two B tiles
+         + 2 * KT_N * sizeof(float)        // centroid norms of the two B tiles
+         + 32 * KT_M * sizeof(float)       // one chunk of coarse distances per point
+         + (size_t)KT_LIST * KT_M * 8      // survivor lists
+         + 64;                             // mbarriers + TMEM slot
+}
+
+__global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTensorParams p) {
+  // SWIZZLE_128B operand tiles need 1024-byte alignment
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int d = p.d, kblocks = d / KT_KBLK;
   const uint32_t tile_bytes = (uint32_t)KT_M * d * 4;            // one operand tile
-  unsigned char *base = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const uint32_t sA = smem_u32(base), sB0 = sA + tile_bytes, sB1 = sB0 + tile_bytes;
-  unsigned char *tail = base + 3 * (size_t)tile_bytes;
-  float *cnb = reinterpret_cast<float *>(tail);                                  // [2][KT_N] centroid norms of the tile
-  int2 *lst = reinterpret_cast<int2 *>(tail + 2 * KT_N * sizeof(float));         // [KT_LIST][KT_M] (index, dist bits)
+  const uint32_t sA = smem_u32(smem_raw), sB0 = sA + tile_bytes, sB1 = sB0 + tile_bytes;
+  float *cnb = reinterpret_cast<float *>(smem_raw + 3 * (size_t)tile_bytes);     // [2][KT_N] centroid norms of the tile
+  float *dsm = cnb + 2 * KT_N;                                                   // [32][KT_M] distances of one chunk
+  int2 *lst = reinterpret_cast<int2 *>(dsm + 32 * KT_M);                         // [KT_LIST][KT_M] (index, dist bits)
   uint64_t *bars = reinterpret_cast<uint64_t *>(lst + KT_LIST * KT_M);           // [2] MMA-done barriers
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, row = threadIdx.x;
+  const int warp = threadIdx.x >> 5, row = threadIdx.x;
   if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
   if (warp == 0) tmem_alloc(tmem_slot, 2 * KT_N);     // two 128-column fp32 accumulator tiles
   tc_fence_before();
@@ -171,13 +180,15 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const K
   uint32_t phase[2] = {0, 0};
 
   const int64_t mtiles = (p.n + KT_M - 1) / KT_M;
+  // operands of the first point tile
+  if ((int64_t)blockIdx.x < mtiles) {
+    load_tile_sw128(sA, p.x, (int64_t)blockIdx.x * KT_M, p.n, d);
+    load_tile_sw128(sB0, p.chi, 0, p.k, d);
+    cp_async_commit();
+  }
   for (int64_t mt = blockIdx.x; mt < mtiles; mt += gridDim.x) {
     const int64_t row0 = mt * KT_M;
-    // ---- A tile and the first B tile
-    load_tile_sw128(sA, p.x, row0, p.n, d);
-    load_tile_sw128(sB0, p.chi, 0, p.k, d);
     if (threadIdx.x < KT_N) cnb[threadIdx.x] = p.cn[threadIdx.x];
-    cp_async_commit();
     cp_async_wait<0>();
     fence_proxy_async();
     __syncthreads();
@@ -217,16 +228,32 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const K
       mbar_wait(&bars[b], phase[b]);     // MMA(t) done: TMEM buffer b is readable, B smem buffer b is free
       phase[b] ^= 1;
       tc_fence_after();
-      // epilogue(t): this thread's point against the 128 centroids of tile t
+      if (t == ntiles - 1 && mt + gridDim.x < mtiles) {
+        // every MMA of this point tile has completed: the operand buffers are free, so the
+        // next point tile's A and first B tile stream in under this last epilogue
+        load_tile_sw128(sA, p.x, (mt + gridDim.x) * KT_M, p.n, d);
+        load_tile_sw128(sB0, p.chi, 0, p.k, d);
+        cp_async_commit();
+      }
+      // epilogue(t): this thread's point against the 128 centroids of tile t.  The hot loop is
+      // branch-free (distance, store, compare, set a bit); hits are handled after the chunk.
       const float *cnt_tile = cnb + b * KT_N;
 #pragma unroll 1
       for (int c = 0; c < KT_N; c += 32) {
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * KT_N + c), v);
+        unsigned hits = 0;
 #pragma unroll
         for (int i = 0; i < 32; i++) {
           const float dist = fmaf(-2.0f, __uint_as_float(v[i]), cnt_tile[c + i]);
-          if (dist <= thr) {
+          dsm[i * KT_M + row] = dist;
+          hits |= (dist <= thr) ? (1u << i) : 0u;
+        }
+        while (hits) {
+          const int i = __ffs(hits) - 1;
+          hits &= hits - 1;
+          const float dist = dsm[i * KT_M + row];
+          if (dist <= thr) {             // the threshold may have tightened inside this chunk
             if (cnt == KT_LIST) cnt = kt_compact(lst, row, thr);
             if (cnt < KT_LIST) lst[(cnt++) * KT_M + row] = make_int2(t * KT_N + c + i, __float_as_int(dist));
             else overflow = 1;
@@ -246,8 +273,8 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const K
     if (row0 + row < p.n) {
       int out[KT_CAND];
       int w = 0;
-      for (int s = 0; s < cnt; s++) {
-        const int2 e = lst[s * KT_M + row];
+      for (int s2 = 0; s2 < cnt; s2++) {
+        const int2 e = lst[s2 * KT_M + row];
         if (__int_as_float(e.y) <= thr) {
           if (w < KT_CAND) out[w] = e.x;
           w++;
@@ -255,16 +282,17 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const K
       }
       if (overflow || w > KT_CAND || w == 0) {
         out[0] = -2;                       // too many to list: stage 2 scans all k
-        for (int s = 1; s < KT_CAND; s++) out[s] = -1;
+        for (int s2 = 1; s2 < KT_CAND; s2++) out[s2] = -1;
       } else {
-        for (int s = w; s < KT_CAND; s++) out[s] = -1;
+        for (int s2 = w; s2 < KT_CAND; s2++) out[s2] = -1;
         for (int a = 1; a < w; a++)        // insertion sort, ascending index (tie rule: lowest j first)
           for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
       }
       *reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND) = make_int4(out[0], out[1], out[2], out[3]);
     }
-    __syncthreads();                       // lst and the operand buffers are reused by the next point tile
+    __syncthreads();                       // lst is reused by the next point tile
   }
+  cp_async_wait<0>();
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_base, 2 * KT_N);
@@ -287,9 +315,22 @@ __global__ void __launch_bounds__(256) km_tensor_cnorm_kernel(const float *__res
 }
 
 // ------------------------------------------------------------------ stage 2: exact kernel
-// One warp per point; lanes split the dimensions.  Survivors are re-evaluated with direct
-// binary32 differences; the binary64 re-score (oracle operation order, one lane, sequential)
-// settles what the error bound cannot.
+// Eight lanes per point (four points per warp); each lane owns d/32 float4 slices of the row.
+// Survivors are re-evaluated with direct binary32 differences; the binary64 re-score (oracle
+// operation order, one lane, sequential) settles what the error bound cannot.
+__device__ __forceinline__ float kt_sum8(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+__device__ __forceinline__ double kt_sum8(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+
 __global__ void __launch_bounds__(256)
 km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, const int *__restrict__ cand,
                         const float *__restrict__ chi, const double *__restrict__ c64, int32_t *__restrict__ labels,
@@ -298,83 +339,128 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
   const double scale_a = st->scale_a, scale_b = st->scale_b, inertia_scale = st->inertia_scale;
   const float tau2 = st->tau_hi;
   const float rho2 = 2.5f * (float)(d + 6) * 0x1.0p-24f;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, g = lane >> 3, sl = lane & 7;
+  const int nq = d >> 5;                                   // float4 slices per lane (1..4)
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   KmThreadScalars S;
   double inertia = 0.0;
-  for (int64_t i = warp0; i < n; i += nwarps) {
-    const float *xr = x + i * (int64_t)d;
-    const int4 cw = *reinterpret_cast<const int4 *>(cand + i * KT_CAND);
-    const int cl[KT_CAND] = {cw.x, cw.y, cw.z, cw.w};
-    const bool scan_all = cl[0] == -2;
-    const int ncand = scan_all ? k : ((cl[1] < 0) ? 1 : (cl[2] < 0) ? 2 : (cl[3] < 0) ? 3 : 4);
-    float b1 = __int_as_float(0x7f800000), b2 = b1;
-    int i1 = scan_all ? 0 : cl[0];
-    if (ncand > 1) {
-      for (int s = 0; s < ncand; s++) {
-        const int j = scan_all ? s : cl[s];
-        const float *cr = chi + (int64_t)j * d;
-        float part = 0.f;
-        for (int t = lane; t < d; t += 32) { const float df = xr[t] - cr[t]; part = fmaf(df, df, part); }
+  for (int64_t base = warp0 * 4; base < n; base += nwarps * 4) {
+    const int64_t i = base + g;
+    const bool live = i < n;
+    const float *xr = x + (live ? i : 0) * (int64_t)d;
+    int4 cw = make_int4(-1, -1, -1, -1);
+    int old = 0;
+    float4 xq[4];
+    if (live) {
+      cw = *reinterpret_cast<const int4 *>(cand + i * KT_CAND);
+      old = labels[i];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        if (part < b1) { b2 = b1; b1 = part; i1 = j; } else if (part < b2) b2 = part;
+      for (int q = 0; q < 4; q++)
+        if (q < nq) xq[q] = *reinterpret_cast<const float4 *>(xr + (q * 8 + sl) * 4);
+    }
+    const bool scan_all = cw.x == -2;
+    const int ncand = !live ? 0 : scan_all ? k : ((cw.y < 0) ? 1 : (cw.z < 0) ? 2 : (cw.w < 0) ? 3 : 4);
+    // a lone survivor is the argmin by the coarse bound: no binary32 pass needed
+    const int nloop = __reduce_max_sync(0xffffffffu, ncand > 1 ? ncand : 0);
+    float b1 = __int_as_float(0x7f800000), b2 = b1;
+    int i1 = scan_all ? 0 : cw.x;
+    for (int s = 0; s < nloop; s++) {
+      const bool act = ncand > 1 && s < ncand;
+      const int j = scan_all ? s : (s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : cw.w);
+      float part = 0.f;
+      if (act) {
+        const float *cr = chi + (int64_t)j * d;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (q < nq) {
+            const float4 cv = *reinterpret_cast<const float4 *>(cr + (q * 8 + sl) * 4);
+            float df = xq[q].x - cv.x; part = fmaf(df, df, part);
+            df = xq[q].y - cv.y; part = fmaf(df, df, part);
+            df = xq[q].z - cv.z; part = fmaf(df, df, part);
+            df = xq[q].w - cv.w; part = fmaf(df, df, part);
+          }
       }
+      part = kt_sum8(part);
+      if (act) { if (part < b1) { b2 = b1; b1 = part; i1 = j; } else if (part < b2) b2 = part; }
     }
     int lab = i1;
-    // a lone survivor is the argmin by the coarse bound; otherwise the binary32 gap must clear its own bound
-    const bool clear = ncand == 1 || (b2 - b1) > fmaf(rho2, b2, tau2);
+    const bool clear = ncand <= 1 || (b2 - b1) > fmaf(rho2, b2, tau2);
     double best = 0.0;
-    if (!clear) {
+    bool have_best = false;
+    if (live && !clear) {
       // binary64, dims ascending, separate multiply and add: the oracle's own arithmetic (A1/A2)
-      if (lane == 0) {
+      if (sl == 0) {
         best = __longlong_as_double(0x7FF0000000000000LL);
         lab = 0;
         for (int s = 0; s < ncand; s++) {
-          const int j = scan_all ? s : cl[s];
+          const int j = scan_all ? s : (s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : cw.w);
           const double dj = km_dist2_f64(xr, c64 + (int64_t)j * d, d);
           if (dj < best) { best = dj; lab = j; }
         }
         S.rescored++;
       }
-      lab = __shfl_sync(0xffffffffu, lab, 0);
-    } else if (exact_inertia) {
-      const double *cr = c64 + (int64_t)lab * d;
-      double part = 0.0;
-      for (int t = lane; t < d; t += 32) { const double df = __dsub_rn((double)xr[t], cr[t]); part = __dadd_rn(part, __dmul_rn(df, df)); }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      best = part;
-    } else {
-      best = (double)b1;
-      if (ncand == 1) {   // no binary32 distance was needed for the decision: take it now
-        const float *cr = chi + (int64_t)lab * d;
-        float part = 0.f;
-        for (int t = lane; t < d; t += 32) { const float df = xr[t] - cr[t]; part = fmaf(df, df, part); }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        best = (double)part;
-      }
+      have_best = true;
     }
-    const int old = labels[i];
-    if (lane == 0) {
+    lab = __shfl_sync(0xffffffffu, lab, g * 8);     // the group's lane 0 holds the decision
+    if (exact_inertia) {
+      double part = 0.0;
+      if (live && !have_best) {
+        const double *cr = c64 + (int64_t)lab * d;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (q < nq) {
+            const double2 c0 = *reinterpret_cast<const double2 *>(cr + (q * 8 + sl) * 4);
+            const double2 c1 = *reinterpret_cast<const double2 *>(cr + (q * 8 + sl) * 4 + 2);
+            double df = __dsub_rn((double)xq[q].x, c0.x); part = __dadd_rn(part, __dmul_rn(df, df));
+            df = __dsub_rn((double)xq[q].y, c0.y); part = __dadd_rn(part, __dmul_rn(df, df));
+            df = __dsub_rn((double)xq[q].z, c1.x); part = __dadd_rn(part, __dmul_rn(df, df));
+            df = __dsub_rn((double)xq[q].w, c1.y); part = __dadd_rn(part, __dmul_rn(df, df));
+          }
+      }
+      part = kt_sum8(part);
+      if (!have_best) best = part;
+    } else if (!have_best) {
+      float part = 0.f;
+      if (live && ncand == 1) {   // no binary32 distance was needed for the decision: take it now
+        const float *cr = chi + (int64_t)lab * d;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (q < nq) {
+            const float4 cv = *reinterpret_cast<const float4 *>(cr + (q * 8 + sl) * 4);
+            float df = xq[q].x - cv.x; part = fmaf(df, df, part);
+            df = xq[q].y - cv.y; part = fmaf(df, df, part);
+            df = xq[q].z - cv.z; part = fmaf(df, df, part);
+            df = xq[q].w - cv.w; part = fmaf(df, df, part);
+          }
+      }
+      part = kt_sum8(part);
+      best = (live && ncand == 1) ? (double)part : (double)b1;
+    }
+    if (live && sl == 0) {
       inertia += best;
       if (lab != old) { S.changed++; labels[i] = lab; }
     }
-    const bool move = incremental ? (lab != old) : true;
+    const bool move = live && (incremental ? (lab != old) : true);
     if (move) {
       const int from = incremental ? old : -1;
-      for (int t = lane; t < d; t += 32) {
-        long long a, b;
-        km_fixed_split((double)xr[t], scale_a, scale_b, a, b);
-        km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
-        km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
-        if (from >= 0) {
-          km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
-          km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
+#pragma unroll
+      for (int q = 0; q < 4; q++)
+        if (q < nq) {
+          const float xv[4] = {xq[q].x, xq[q].y, xq[q].z, xq[q].w};
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int t = (q * 8 + sl) * 4 + u;
+            long long a, b;
+            km_fixed_split((double)xv[u], scale_a, scale_b, a, b);
+            km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
+            km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
+            if (from >= 0) {
+              km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
+              km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
+            }
+          }
         }
-      }
-      if (lane == 0) {
+      if (sl == 0) {
         km_atomic_add_ll(acc + L.cnt + lab, 1);
         if (from >= 0) km_atomic_add_ll(acc + L.cnt + from, -1);
       }
@@ -387,8 +473,7 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
 // ------------------------------------------------------------------ launcher
 bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin) {
   if (dtype != KM_DTYPE_F32 || d % KT_KBLK != 0 || d < KT_KBLK || d > 128 || k < 2) return false;
-  const size_t smem = 3 * (size_t)KT_M * d * 4 + 2 * KT_N * 4 + (size_t)KT_LIST * KT_M * 8 + 64 + 1024;
-  return smem <= (size_t)max_smem_optin;
+  return kt_smem_bytes(d) <= (size_t)max_smem_optin;
 }
 
 cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
@@ -401,18 +486,21 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
     KmTensorParams p;
     p.x = (const float *)a.x; p.n = a.n; p.d = a.d; p.k = a.k; p.chi = a.chi; p.cn = a.t_cn; p.st = a.state;
     p.xnmax = a.t_xnmax; p.cand = a.t_cand;
-    const size_t smem = 3 * (size_t)KT_M * a.d * 4 + 2 * KT_N * 4 + (size_t)KT_LIST * KT_M * 8 + 64 + 1024;
+    const size_t smem = kt_smem_bytes(a.d);
     e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    // two CTAs per SM when shared memory allows (each holds 256 of the SM's 512 TMEM columns)
+    const int per_sm = (2 * (smem + 1024) <= (size_t)a.max_smem_optin) ? 2 : 1;
     const int64_t mtiles = (a.n + KT_M - 1) / KT_M;
-    const int grid = (int)(mtiles < a.sm_count ? mtiles : a.sm_count);
+    const int64_t cap = (int64_t)a.sm_count * per_sm;
+    const int grid = (int)(mtiles < cap ? mtiles : cap);
     km_tensor_coarse_kernel<<<grid, KT_THREADS, smem, a.stream>>>(p);
     (*launches)++;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const int64_t want = (a.n * 32 + 255) / 256;
-    const int64_t cap = (int64_t)a.sm_count * 8;
-    km_tensor_stage2_kernel<<<(int)(want < cap ? want : cap), 256, 0, a.stream>>>(
+    const int64_t want = (a.n * 8 + 255) / 256;
+    const int64_t cap2 = (int64_t)a.sm_count * 8;
+    km_tensor_stage2_kernel<<<(int)(want < cap2 ? want : cap2), 256, 0, a.stream>>>(
         (const float *)a.x, a.n, a.d, a.k, a.t_cand, a.chi, a.c64, a.labels, a.acc, a.state, a.incremental, a.exact_inertia);
     (*launches)++;
   }
