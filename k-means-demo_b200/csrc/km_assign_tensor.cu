@@ -125,6 +125,7 @@ struct KmTensorParams {
   const KmState *st;   // st->cnmax2 = max_j |chi_j|^2
   float xnmax;         // upper bound of |x_i| over the job
   int *cand;           // [n][KT_CAND]: survivors (ascending index), -1 = unused; cand[i][0] = -2: scan all k
+  const int32_t *labels;  // previous labels: the old centroid's distance seeds the running minimum
 };
 
 // Copy `rows` x d floats (row stride d) into the swizzled K-major layout the UMMA descriptor
@@ -132,11 +133,15 @@ struct KmTensorParams {
 // Rows at or beyond `valid` are zero-filled (cp.async with src-size 0).
 __device__ __forceinline__ void load_tile_sw128(uint32_t smem_base, const float *g, int64_t row0, int64_t valid_rows,
                                                 int d) {
-  const int chunks_per_row = d >> 2;
-  const int total = KT_M * chunks_per_row;
-  for (int c = threadIdx.x; c < total; c += KT_THREADS) {
-    const int r = c / chunks_per_row, q = c - r * chunks_per_row;
-    const int kb = q >> 3, ch = q & 7;
+  // lanes sweep the 16-byte chunks of a row (d/4 of them: 8, 16, 24 or 32), several rows per
+  // warp pass when a row is shorter than a warp; nothing in the loop divides
+  const int cpr = d >> 2;
+  const int rpp = 32 / cpr;                       // rows per warp pass (1 for d = 96, 128)
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r_off = lane / cpr, q = lane - r_off * cpr;
+  if (r_off >= rpp) return;                       // d = 96: lanes 24..31 idle
+  const int kb = q >> 3, ch = q & 7;
+  for (int r = warp * rpp + r_off; r < KT_M; r += (KT_THREADS / 32) * rpp) {
     const uint32_t dst = smem_base + kb * (KT_M * 128) + r * 128 + ((ch ^ (r & 7)) << 4);
     const bool ok = row0 + r < valid_rows;
     const float *src = g + (ok ? (row0 + r) * (int64_t)d + q * 4 : 0);
@@ -148,7 +153,7 @@ __device__ __forceinline__ void load_tile_sw128(uint32_t smem_base, const float 
 static __host__ __device__ inline size_t kt_smem_bytes(int d) {
   return 3 * (size_t)KT_M * d * 4          // A tile + two B tiles
          + 2 * KT_N * sizeof(float)        // centroid norms of the two B tiles
-         + 32 * KT_M * sizeof(float)       // one chunk of coarse distances per point
+         + 36 * KT_M * sizeof(float)       // one chunk of coarse distances per point (row stride 36)
          + (size_t)KT_LIST * KT_M * 8      // survivor lists
          + 64;                             // mbarriers + TMEM slot
 }
@@ -160,8 +165,8 @@ __global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTe
   const uint32_t tile_bytes = (uint32_t)KT_M * d * 4;            // one operand tile
   const uint32_t sA = smem_u32(smem_raw), sB0 = sA + tile_bytes, sB1 = sB0 + tile_bytes;
   float *cnb = reinterpret_cast<float *>(smem_raw + 3 * (size_t)tile_bytes);     // [2][KT_N] centroid norms of the tile
-  float *dsm = cnb + 2 * KT_N;                                                   // [32][KT_M] distances of one chunk
-  int2 *lst = reinterpret_cast<int2 *>(dsm + 32 * KT_M);                         // [KT_LIST][KT_M] (index, dist bits)
+  float *dsm = cnb + 2 * KT_N;                                                   // [KT_M][36] distances of one chunk
+  int2 *lst = reinterpret_cast<int2 *>(dsm + 36 * KT_M);                         // [KT_LIST][KT_M] (index, dist bits)
   uint64_t *bars = reinterpret_cast<uint64_t *>(lst + KT_LIST * KT_M);           // [2] MMA-done barriers
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
 
@@ -205,7 +210,31 @@ __global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTe
       if (threadIdx.x < KT_N) cnb[KT_N + threadIdx.x] = p.cn[KT_N + threadIdx.x];
       cp_async_commit();
     }
+    // Seed the running minimum with the coarse distance to the point's PREVIOUS centroid
+    // (binary32 dot product of this thread's row of the A tile with chi[old], + E for the
+    // TF32 stage's own error): the true minimum can only be lower, so nothing is lost, and the
+    // threshold is tight from the first centroid tile on instead of after the nearest one
+    // happens to stream by.
     float runmin = __int_as_float(0x7f800000), thr = runmin;
+    {
+      const int old = (row0 + row < p.n) ? p.labels[row0 + row] : -1;
+      if (old >= 0 && old < p.k) {
+        const float *cr = p.chi + (int64_t)old * d;
+        float dot = 0.f;
+        for (int kb = 0; kb < kblocks; kb++) {
+          const unsigned char *arow = smem_raw + kb * (KT_M * 128) + row * 128;
+#pragma unroll
+          for (int ch = 0; ch < 8; ch++) {
+            const float4 xv = *reinterpret_cast<const float4 *>(arow + ((ch ^ (row & 7)) << 4));
+            const float4 cv = __ldg(reinterpret_cast<const float4 *>(cr + kb * 32 + ch * 4));
+            dot = fmaf(xv.x, cv.x, dot); dot = fmaf(xv.y, cv.y, dot);
+            dot = fmaf(xv.z, cv.z, dot); dot = fmaf(xv.w, cv.w, dot);
+          }
+        }
+        runmin = fmaf(-2.0f, dot, p.cn[old]) + 0.5f * two_e;
+        thr = runmin + two_e;
+      }
+    }
     int cnt = 0, overflow = 0;
 
     for (int t = 0; t < ntiles; t++) {
@@ -243,16 +272,25 @@ __global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTe
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(b * KT_N + c), v);
         unsigned hits = 0;
+        float *drow = dsm + row * 36;
 #pragma unroll
-        for (int i = 0; i < 32; i++) {
-          const float dist = fmaf(-2.0f, __uint_as_float(v[i]), cnt_tile[c + i]);
-          dsm[i * KT_M + row] = dist;
-          hits |= (dist <= thr) ? (1u << i) : 0u;
+        for (int i4 = 0; i4 < 8; i4++) {
+          const float4 cn4 = *reinterpret_cast<const float4 *>(cnt_tile + c + i4 * 4);   // warp-uniform: one broadcast LDS.128
+          float4 d4;
+          d4.x = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 0]), cn4.x);
+          d4.y = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 1]), cn4.y);
+          d4.z = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 2]), cn4.z);
+          d4.w = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 3]), cn4.w);
+          *reinterpret_cast<float4 *>(drow + i4 * 4) = d4;
+          if (d4.x <= thr) hits |= 1u << (i4 * 4 + 0);
+          if (d4.y <= thr) hits |= 1u << (i4 * 4 + 1);
+          if (d4.z <= thr) hits |= 1u << (i4 * 4 + 2);
+          if (d4.w <= thr) hits |= 1u << (i4 * 4 + 3);
         }
         while (hits) {
           const int i = __ffs(hits) - 1;
           hits &= hits - 1;
-          const float dist = dsm[i * KT_M + row];
+          const float dist = drow[i];
           if (dist <= thr) {             // the threshold may have tightened inside this chunk
             if (cnt == KT_LIST) cnt = kt_compact(lst, row, thr);
             if (cnt < KT_LIST) lst[(cnt++) * KT_M + row] = make_int2(t * KT_N + c + i, __float_as_int(dist));
@@ -442,24 +480,18 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
     }
     const bool move = live && (incremental ? (lab != old) : true);
     if (move) {
+      // consecutive lanes take consecutive dimensions: 8 lanes = 64 contiguous bytes per limb row
       const int from = incremental ? old : -1;
-#pragma unroll
-      for (int q = 0; q < 4; q++)
-        if (q < nq) {
-          const float xv[4] = {xq[q].x, xq[q].y, xq[q].z, xq[q].w};
-#pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const int t = (q * 8 + sl) * 4 + u;
-            long long a, b;
-            km_fixed_split((double)xv[u], scale_a, scale_b, a, b);
-            km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
-            km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
-            if (from >= 0) {
-              km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
-              km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
-            }
-          }
+      for (int t = sl; t < d; t += 8) {
+        long long a, b;
+        km_fixed_split((double)xr[t], scale_a, scale_b, a, b);
+        km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
+        km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
+        if (from >= 0) {
+          km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
+          km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
         }
+      }
       if (sl == 0) {
         km_atomic_add_ll(acc + L.cnt + lab, 1);
         if (from >= 0) km_atomic_add_ll(acc + L.cnt + from, -1);
@@ -485,7 +517,7 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   if (a.n > 0) {
     KmTensorParams p;
     p.x = (const float *)a.x; p.n = a.n; p.d = a.d; p.k = a.k; p.chi = a.chi; p.cn = a.t_cn; p.st = a.state;
-    p.xnmax = a.t_xnmax; p.cand = a.t_cand;
+    p.xnmax = a.t_xnmax; p.cand = a.t_cand; p.labels = a.labels;
     const size_t smem = kt_smem_bytes(a.d);
     e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
