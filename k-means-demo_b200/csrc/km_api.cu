@@ -109,7 +109,8 @@ static void free_centroids(km_ctx *ctx) {
   for (int q = 0; q < 2; q++) { if (ctx->p1S[q]) cudaFree(ctx->p1S[q]); if (ctx->p1C[q]) cudaFree(ctx->p1C[q]); ctx->p1S[q] = nullptr; ctx->p1C[q] = nullptr; }
   for (int q = 0; q < 3; q++) { if (ctx->p1D[q]) cudaFree(ctx->p1D[q]); ctx->p1D[q] = nullptr; }
   if (ctx->t_cn) cudaFree(ctx->t_cn);
-  ctx->t_cn = nullptr;
+  if (ctx->t_cbf) cudaFree(ctx->t_cbf);
+  ctx->t_cn = nullptr; ctx->t_cbf = nullptr;
   ctx->p1 = false; ctx->p1_pending = false;
   ctx->have_centroids = false; ctx->k = 0; ctx->acc_len = 0;
 }
@@ -552,7 +553,10 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
       KM_CUDA(ctx, cudaMalloc(&ctx->acc, (size_t)L.len * sizeof(long long)));
       if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
       else ctx->acc_global = ctx->acc;
-      if (path == KM_PATH_TENSOR) KM_CUDA(ctx, cudaMalloc(&ctx->t_cn, ((size_t)k + 512) * sizeof(float)));
+      if (path == KM_PATH_TENSOR) {
+        KM_CUDA(ctx, cudaMalloc(&ctx->t_cn, ((size_t)k + 512) * sizeof(float)));
+        KM_CUDA(ctx, cudaMalloc(&ctx->t_cbf, km_tensor_cbf_bytes(d, k)));
+      }
     }
     ctx->k = k;
     ctx->acc_len = L.len;
@@ -660,7 +664,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.scale_b = ldexp(1.0, ctx->QB);
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
-  a.t_cn = nullptr; a.t_cand = nullptr; a.t_xnmax = 0.f;
+  a.t_cn = nullptr; a.t_cbf = nullptr; a.t_cand = nullptr; a.t_xnmax = 0.f;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
@@ -688,7 +692,7 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
       KM_CUDA(ctx, cudaMalloc(&ctx->t_cand, std::max<size_t>((size_t)ctx->n * KT_CAND * sizeof(int), 16)));
       ctx->t_cand_n = ctx->n;
     }
-    a.t_cn = ctx->t_cn; a.t_cand = ctx->t_cand;
+    a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_cand = ctx->t_cand;
     a.t_xnmax = (float)(sqrt((double)ctx->d) * ctx->maxabs * (1.0 + 1e-6));
     KM_CUDA(ctx, km_launch_assign_tensor(a, &ctx->launches));
     ctx->last_path = KM_PATH_TENSOR;

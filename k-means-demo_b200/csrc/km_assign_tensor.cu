@@ -21,6 +21,9 @@
 //     (global int64 atomics), change count and inertia follow.
 //
 // So the labels are the oracle's bit for bit, and the tensor cores do all O(N k d) work.
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
 #include "km_commit.cuh"
 #include "km_internal.h"
 
@@ -105,12 +108,24 @@ __device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// same, BF16 inputs (kind::f16), K = 16 per instruction
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
 // rare: the survivor list of a point is full -> drop what the tighter threshold has since excluded
-__device__ __noinline__ int kt_compact(int2 *lst, int row, float thr) {
+__device__ __noinline__ int kt_compact(int2 *lst, int row, float thr, int stride = KT_M) {
   int w = 0;
   for (int s = 0; s < KT_LIST; s++) {
-    const int2 e = lst[s * KT_M + row];
-    if (__int_as_float(e.y) <= thr) lst[(w++) * KT_M + row] = e;
+    const int2 e = lst[s * stride + row];
+    if (__int_as_float(e.y) <= thr) lst[(w++) * stride + row] = e;
   }
   return w;
 }
@@ -336,14 +351,236 @@ __global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTe
   if (warp == 0) tmem_dealloc(tmem_base, 2 * KT_N);
 }
 
+// ------------------------------------------------------------------ stage 1, BF16, two point tiles per CTA
+// The production coarse kernel.  Differences from the TF32 kernel above:
+//   * operands are BF16 (x converted on the way into shared memory, centroids pre-converted
+//     once per pass): half the shared memory per tile and twice the MMA rate;
+//   * a CTA holds TWO point tiles (256 points, 8 warps, all 512 TMEM columns as 2 x 2
+//     accumulator buffers), so every centroid tile streamed from L2 feeds two MMAs — half the
+//     L2 traffic per point — and the SM has 8 epilogue warps instead of 4.
+// E grows to 2^-6.5 |x||c| (BF16 keeps 8 significant bits, round to nearest); everything
+// downstream (survivor lists, stage 2) is unchanged.
+#define KB_THREADS 256
+#define KB_MT 2
+
+static __host__ __device__ inline int kb_kblocks(int d) { return (d + 63) / 64; }
+static __host__ __device__ inline size_t kb_smem_bytes(int d) {
+  return (size_t)(KB_MT + 2) * kb_kblocks(d) * (KT_M * 128)   // two A tiles + two B buffers
+         + 2 * KT_N * sizeof(float) + 36 * (KB_MT * KT_M) * sizeof(float) + (size_t)KT_LIST * (KB_MT * KT_M) * 8 + 64;
+}
+
+struct KmTensorBf16Params {
+  KmTensorParams base;
+  const __nv_bfloat16 *cbf;   // [kpad][dpad] BF16 centroids, zero padded
+  int dpad;                   // kblocks * 64
+};
+
+__global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(const KmTensorBf16Params pp) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const KmTensorParams &p = pp.base;
+  const int d = p.d, kblocks = kb_kblocks(d), dpad = pp.dpad;
+  constexpr int ROWS = KB_MT * KT_M;                       // 256 points per CTA pass
+  const uint32_t kb_bytes = KT_M * 128;                    // one 64-element k-block of one 128-row tile
+  const uint32_t tile_bytes = kblocks * kb_bytes;
+  const uint32_t sA = smem_u32(smem_raw), sB0 = sA + KB_MT * tile_bytes, sB1 = sB0 + tile_bytes;
+  float *cnb = reinterpret_cast<float *>(smem_raw + (KB_MT + 2) * (size_t)tile_bytes);
+  float *dsm = cnb + 2 * KT_N;                                                   // [ROWS][36]
+  int2 *lst = reinterpret_cast<int2 *>(dsm + 36 * ROWS);                         // [KT_LIST][ROWS]
+  uint64_t *bars = reinterpret_cast<uint64_t *>(lst + KT_LIST * ROWS);
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, row = threadIdx.x;
+  const int mi = warp >> 2, quad = warp & 3;               // point tile and TMEM lane quadrant of this warp
+  // zero the A region once: the padding columns (d..dpad) are never written again
+  for (uint32_t o = threadIdx.x * 16; o < KB_MT * tile_bytes; o += KB_THREADS * 16)
+    *reinterpret_cast<uint4 *>(smem_raw + o) = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+  if (warp == 0) tmem_alloc(tmem_slot, 512);              // 2 point tiles x 2 buffers x 128 columns
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t idesc = umma_idesc_bf16(KT_M, KT_N);
+  const int ntiles = (p.k + KT_N - 1) / KT_N;
+  const float cnmax = sqrtf(p.st->cnmax2);
+  const float two_e = 2.0f * (0.011049f * p.xnmax * cnmax) + 1e-6f * (p.xnmax * p.xnmax + p.st->cnmax2);
+  uint32_t phase[2] = {0, 0};
+
+  // x rows -> BF16, swizzled K-major (two tiles); lanes sweep float4 chunks, warps sweep rows
+  auto load_a = [&](int64_t row0) {
+    const int cpr = d >> 2, rpp = 32 / cpr, r_off = lane / cpr, q = lane - r_off * cpr;
+    if (r_off >= rpp) return;
+    const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
+    for (int r = warp * rpp + r_off; r < ROWS; r += (KB_THREADS / 32) * rpp) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row0 + r < p.n) v = __ldg(reinterpret_cast<const float4 *>(p.x + (row0 + r) * (int64_t)d + e));
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+      const int rr = r & (KT_M - 1);
+      unsigned char *dst = smem_raw + (r >> 7) * tile_bytes + kb * kb_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4) + within;
+      *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
+    }
+  };
+  auto load_b = [&](uint32_t sB, int64_t j0) {
+    const int cpr = dpad >> 3, rpp = 32 / cpr, r_off = lane / cpr, q = lane - r_off * cpr;   // 16-byte chunks of 8 BF16
+    const int kb = q >> 3, ch = q & 7;
+    for (int r = warp * rpp + r_off; r < KT_N; r += (KB_THREADS / 32) * rpp)
+      cp_async16(sB + kb * kb_bytes + r * 128 + ((ch ^ (r & 7)) << 4), pp.cbf + (j0 + r) * (int64_t)dpad + q * 8, 16);
+  };
+  auto issue_mma = [&](uint32_t sB, int b) {
+    for (int m = 0; m < KB_MT; m++)
+      for (int kb = 0; kb < kblocks; kb++)
+        for (int ks = 0; ks < 4; ks++)
+          umma_bf16(tmem_base + (uint32_t)((m * 2 + b) * KT_N), umma_desc_sw128(sA + m * tile_bytes + kb * kb_bytes + ks * 32),
+                    umma_desc_sw128(sB + kb * kb_bytes + ks * 32), idesc, (kb | ks) != 0);
+    umma_commit(&bars[b]);
+  };
+
+  const int64_t passes = (p.n + ROWS - 1) / ROWS;
+  if ((int64_t)blockIdx.x < passes) {
+    load_a((int64_t)blockIdx.x * ROWS);
+    load_b(sB0, 0);
+    cp_async_commit();
+  }
+  for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
+    const int64_t row0 = ps * ROWS;
+    if (threadIdx.x < KT_N) cnb[threadIdx.x] = p.cn[threadIdx.x];
+    cp_async_wait<0>();
+    fence_proxy_async();
+    __syncthreads();
+    if (threadIdx.x == 0) { tc_fence_after(); issue_mma(sB0, 0); }
+    if (ntiles > 1) {
+      load_b(sB1, KT_N);
+      if (threadIdx.x < KT_N) cnb[KT_N + threadIdx.x] = p.cn[KT_N + threadIdx.x];
+      cp_async_commit();
+    }
+    // seed the running minimum with the coarse distance to the previous centroid (see above)
+    float runmin = __int_as_float(0x7f800000), thr = runmin;
+    {
+      const int old = (row0 + row < p.n) ? p.labels[row0 + row] : -1;
+      if (old >= 0 && old < p.k) {
+        const __nv_bfloat16 *cr = pp.cbf + (int64_t)old * dpad;
+        const int rr = row & (KT_M - 1);
+        float dot = 0.f;
+        for (int kb = 0; kb < kblocks; kb++) {
+          const unsigned char *arow = smem_raw + mi * tile_bytes + kb * kb_bytes + rr * 128;
+#pragma unroll
+          for (int ch = 0; ch < 8; ch++) {
+            const uint4 xa = *reinterpret_cast<const uint4 *>(arow + ((ch ^ (rr & 7)) << 4));
+            const uint4 cb = __ldg(reinterpret_cast<const uint4 *>(cr + kb * 64 + ch * 8));
+            const unsigned xw[4] = {xa.x, xa.y, xa.z, xa.w}, cw[4] = {cb.x, cb.y, cb.z, cb.w};
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const float2 xf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&xw[u]));
+              const float2 cf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&cw[u]));
+              dot = fmaf(xf.x, cf.x, dot);
+              dot = fmaf(xf.y, cf.y, dot);
+            }
+          }
+        }
+        runmin = fmaf(-2.0f, dot, p.cn[old]) + 0.5f * two_e;
+        thr = runmin + two_e;
+      }
+    }
+    int cnt = 0, overflow = 0;
+
+    for (int t = 0; t < ntiles; t++) {
+      const int b = t & 1;
+      if (t + 1 < ntiles) {
+        cp_async_wait<0>();
+        fence_proxy_async();
+        __syncthreads();
+        if (threadIdx.x == 0) { tc_fence_after(); issue_mma(b ? sB0 : sB1, b ^ 1); }
+      }
+      mbar_wait(&bars[b], phase[b]);
+      phase[b] ^= 1;
+      tc_fence_after();
+      if (t == ntiles - 1 && ps + gridDim.x < passes) {
+        // all MMAs of this pass are done: the next pass's operands stream in under this epilogue
+        load_a((ps + gridDim.x) * ROWS);
+        load_b(sB0, 0);
+        cp_async_commit();
+      }
+      const float *cnt_tile = cnb + b * KT_N;
+      float *drow = dsm + row * 36;
+#pragma unroll 1
+      for (int c = 0; c < KT_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((mi * 2 + b) * KT_N + c), v);
+        unsigned hits = 0;
+#pragma unroll
+        for (int i4 = 0; i4 < 8; i4++) {
+          const float4 cn4 = *reinterpret_cast<const float4 *>(cnt_tile + c + i4 * 4);
+          float4 d4;
+          d4.x = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 0]), cn4.x);
+          d4.y = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 1]), cn4.y);
+          d4.z = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 2]), cn4.z);
+          d4.w = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 3]), cn4.w);
+          *reinterpret_cast<float4 *>(drow + i4 * 4) = d4;
+          if (d4.x <= thr) hits |= 1u << (i4 * 4 + 0);
+          if (d4.y <= thr) hits |= 1u << (i4 * 4 + 1);
+          if (d4.z <= thr) hits |= 1u << (i4 * 4 + 2);
+          if (d4.w <= thr) hits |= 1u << (i4 * 4 + 3);
+        }
+        while (hits) {
+          const int i = __ffs(hits) - 1;
+          hits &= hits - 1;
+          const float dist = drow[i];
+          if (dist <= thr) {
+            if (cnt == KT_LIST) cnt = kt_compact(lst, row, thr, ROWS);
+            if (cnt < KT_LIST) lst[(cnt++) * ROWS + row] = make_int2(t * KT_N + c + i, __float_as_int(dist));
+            else overflow = 1;
+            if (dist < runmin) { runmin = dist; thr = runmin + two_e; }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncthreads();
+      if (t + 2 < ntiles) {
+        load_b(b ? sB1 : sB0, (int64_t)(t + 2) * KT_N);
+        if (threadIdx.x < KT_N) cnb[b * KT_N + threadIdx.x] = p.cn[(t + 2) * KT_N + threadIdx.x];
+        cp_async_commit();
+      }
+    }
+    if (row0 + row < p.n) {
+      int out[KT_CAND];
+      int w = 0;
+      for (int s2 = 0; s2 < cnt; s2++) {
+        const int2 e = lst[s2 * ROWS + row];
+        if (__int_as_float(e.y) <= thr) {
+          if (w < KT_CAND) out[w] = e.x;
+          w++;
+        }
+      }
+      if (overflow || w > KT_CAND || w == 0) {
+        out[0] = -2;
+        for (int s2 = 1; s2 < KT_CAND; s2++) out[s2] = -1;
+      } else {
+        for (int s2 = w; s2 < KT_CAND; s2++) out[s2] = -1;
+        for (int a = 1; a < w; a++)
+          for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
+      }
+      *reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND) = make_int4(out[0], out[1], out[2], out[3]);
+    }
+    __syncthreads();
+  }
+  cp_async_wait<0>();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+
 // |chi_j|^2 per centroid (padded with +inf to a whole number of MMA tiles) and its maximum
 __global__ void __launch_bounds__(256) km_tensor_cnorm_kernel(const float *__restrict__ chi, int k, int d, int kpad,
-                                                              float *__restrict__ cn, KmState *st) {
+                                                              float *__restrict__ cn, KmState *st,
+                                                              __nv_bfloat16 *__restrict__ cbf, int dpad) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= kpad) return;
   float s = 0.f;
   if (warp < k)
     for (int t = lane; t < d; t += 32) { const float v = chi[(int64_t)warp * d + t]; s = fmaf(v, v, s); }
+  if (cbf)   // BF16 copy of the row, zero beyond d and beyond k
+    for (int t = lane; t < dpad; t += 32)
+      cbf[(int64_t)warp * dpad + t] = __float2bfloat16_rn((warp < k && t < d) ? chi[(int64_t)warp * d + t] : 0.f);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) {
@@ -503,30 +740,48 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
 }
 
 // ------------------------------------------------------------------ launcher
+
 bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin) {
   if (dtype != KM_DTYPE_F32 || d % KT_KBLK != 0 || d < KT_KBLK || d > 128 || k < 2) return false;
-  return kt_smem_bytes(d) <= (size_t)max_smem_optin;
+  return kt_smem_bytes(d) <= (size_t)max_smem_optin && kb_smem_bytes(d) <= (size_t)max_smem_optin;
+}
+
+size_t km_tensor_cbf_bytes(int32_t d, int32_t k) {
+  const int kpad = ((k + KT_N - 1) / KT_N + 2) * KT_N;
+  return (size_t)kpad * kb_kblocks(d) * 64 * sizeof(__nv_bfloat16);
 }
 
 cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   const int kpad = ((a.k + KT_N - 1) / KT_N + 2) * KT_N;   // whole tiles, plus slack for the prefetch of cn
+  static const bool use_tf32 = getenv("KM_TENSOR_TF32") != nullptr;   // A/B switch for measurements
+  const int dpad = kb_kblocks(a.d) * 64;
   cudaError_t e = cudaMemsetAsync(&a.state->cnmax2, 0, sizeof(float), a.stream);
   if (e != cudaSuccess) return e;
-  km_tensor_cnorm_kernel<<<(kpad * 32 + 255) / 256, 256, 0, a.stream>>>(a.chi, a.k, a.d, kpad, a.t_cn, a.state);
+  km_tensor_cnorm_kernel<<<(kpad * 32 + 255) / 256, 256, 0, a.stream>>>(a.chi, a.k, a.d, kpad, a.t_cn, a.state,
+                                                                        use_tf32 ? nullptr : (__nv_bfloat16 *)a.t_cbf, dpad);
   (*launches)++;
   if (a.n > 0) {
     KmTensorParams p;
     p.x = (const float *)a.x; p.n = a.n; p.d = a.d; p.k = a.k; p.chi = a.chi; p.cn = a.t_cn; p.st = a.state;
     p.xnmax = a.t_xnmax; p.cand = a.t_cand; p.labels = a.labels;
-    const size_t smem = kt_smem_bytes(a.d);
-    e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    // two CTAs per SM when shared memory allows (each holds 256 of the SM's 512 TMEM columns)
-    const int per_sm = (2 * (smem + 1024) <= (size_t)a.max_smem_optin) ? 2 : 1;
-    const int64_t mtiles = (a.n + KT_M - 1) / KT_M;
-    const int64_t cap = (int64_t)a.sm_count * per_sm;
-    const int grid = (int)(mtiles < cap ? mtiles : cap);
-    km_tensor_coarse_kernel<<<grid, KT_THREADS, smem, a.stream>>>(p);
+    if (use_tf32) {
+      const size_t smem = kt_smem_bytes(a.d);
+      e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      // two CTAs per SM when shared memory allows (each holds 256 of the SM's 512 TMEM columns)
+      const int per_sm = (2 * (smem + 1024) <= (size_t)a.max_smem_optin) ? 2 : 1;
+      const int64_t mtiles = (a.n + KT_M - 1) / KT_M;
+      const int64_t cap = (int64_t)a.sm_count * per_sm;
+      km_tensor_coarse_kernel<<<(int)(mtiles < cap ? mtiles : cap), KT_THREADS, smem, a.stream>>>(p);
+    } else {
+      KmTensorBf16Params pp;
+      pp.base = p; pp.cbf = (const __nv_bfloat16 *)a.t_cbf; pp.dpad = dpad;
+      const size_t smem = kb_smem_bytes(a.d);
+      e = cudaFuncSetAttribute(km_tensor_coarse_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      const int64_t passes = (a.n + KB_MT * KT_M - 1) / (KB_MT * KT_M);
+      km_tensor_coarse_bf16_kernel<<<(int)(passes < a.sm_count ? passes : a.sm_count), KB_THREADS, smem, a.stream>>>(pp);
+    }
     (*launches)++;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -55,16 +55,16 @@ __device__ __forceinline__ void km_refresh_scales(KmState *st, double cmax, doub
   st->tau_hi = r.tau_hi;
 }
 
-// All threads of exactly one block call this.
-__device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
+// Part 1: the elements [first, kd) in steps of `stride`: c = S / count (or unchanged), the
+// binary32 hi/lo copies; returns this thread's max |c|.
+__device__ __forceinline__ double km_finalize_elements(const KmFinalizeArgs &f, int64_t first, int64_t stride,
+                                                       long long changed) {
   const KmAccLayout L = km_acc_layout(f.k, f.d);
-  const bool reads = f.do_stats || f.do_update;
-  const long long changed = reads ? __ldcg(f.acc_in + L.scal + KM_ACC_CHANGED) : 0;
   const bool upd = f.do_update && (!f.update_needs_change || changed > 0);
   const int QB = f.st->QB, shift = f.st->qa + f.st->QB;
   const int64_t kd = (int64_t)f.k * f.d;
   double lmax = 0.0;
-  for (int64_t idx = threadIdx.x; idx < kd; idx += blockDim.x) {
+  for (int64_t idx = first; idx < kd; idx += stride) {
     double c = f.c64[idx];
     if (upd) {
       const long long cnt = __ldcg(f.acc_in + L.cnt + idx / f.d);
@@ -79,15 +79,14 @@ __device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
     f.clo[idx] = __double2float_rn(__dsub_rn(c, (double)h));
     lmax = fmax(lmax, fabs(c));
   }
-  __shared__ double red[32];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = lmax;
-  __syncthreads();
-  if (threadIdx.x != 0) return;
-  const int nwarps = (blockDim.x + 31) >> 5;
-  double cmax = 0.0;
-  for (int w = 0; w < nwarps; w++) cmax = fmax(cmax, red[w]);
+  return lmax;
+}
+
+// Part 2 (one thread): publish the pass's stats, clear the per-pass scalars, refresh the scales.
+__device__ __forceinline__ void km_finalize_publish(const KmFinalizeArgs &f, double cmax, long long changed) {
+  const KmAccLayout L = km_acc_layout(f.k, f.d);
+  const bool upd = f.do_update && (!f.update_needs_change || changed > 0);
+  const int QB = f.st->QB;
   const int qi_used = f.st->qi;  // the scale the assignment just used
   if (f.do_stats) {
     f.st->it += 1;
@@ -103,5 +102,44 @@ __device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
     if (f.slot) *f.slot = s;  // pinned host memory; visible to the host once the kernel's event completes
   }
   km_refresh_scales(f.st, cmax, f.maxabs_x, f.d);
+}
+
+// All threads of exactly one block call this.
+__device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
+  const KmAccLayout L = km_acc_layout(f.k, f.d);
+  const bool reads = f.do_stats || f.do_update;
+  const long long changed = reads ? __ldcg(f.acc_in + L.scal + KM_ACC_CHANGED) : 0;
+  double lmax = km_finalize_elements(f, threadIdx.x, blockDim.x, changed);
+  __shared__ double red[32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = lmax;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  double cmax = 0.0;
+  for (int w = 0; w < nwarps; w++) cmax = fmax(cmax, red[w]);
+  km_finalize_publish(f, cmax, changed);
+}
+
+// Many blocks (large k*d): block maxima meet in st->cmax_bits, the last block to finish publishes.
+__device__ __forceinline__ void km_finalize_grid(const KmFinalizeArgs &f) {
+  const KmAccLayout L = km_acc_layout(f.k, f.d);
+  const bool reads = f.do_stats || f.do_update;
+  const long long changed = reads ? __ldcg(f.acc_in + L.scal + KM_ACC_CHANGED) : 0;
+  double lmax = km_finalize_elements(f, (int64_t)blockIdx.x * blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x, changed);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+  if ((threadIdx.x & 31) == 0 && lmax > 0.0) atomicMax(&f.st->cmax_bits, (unsigned long long)__double_as_longlong(lmax));
+  __shared__ int is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(&f.st->ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last || threadIdx.x != 0) return;
+  __threadfence();
+  const unsigned long long bits = atomicExch(&f.st->cmax_bits, 0ULL);
+  f.st->ticket = 0;
+  km_finalize_publish(f, __longlong_as_double((long long)bits), changed);
 }
 #endif

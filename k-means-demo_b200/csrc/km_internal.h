@@ -81,6 +81,7 @@ struct km_ctx {
 
   // ---- tensor path scratch
   float *t_cn = nullptr;
+  void *t_cbf = nullptr;
   int *t_cand = nullptr;
   int64_t t_cand_n = 0;
   int path_now = 0;                 // KM_PATH_* chosen for the current (points, centroids)
@@ -109,6 +110,7 @@ struct KmAssignArgs {
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
   float *t_cn;         // tensor path: |chi_j|^2 (padded)
+  void *t_cbf;         // tensor path: BF16 copy of the centroids, [kpad][dpad]
   int *t_cand;         // tensor path: [n][KT_CAND] survivors of the coarse stage
   float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
@@ -121,6 +123,7 @@ cudaError_t km_launch_assign_direct(const KmAssignArgs &a, int64_t *launches);
 cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches);
 cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches);
 bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
+size_t km_tensor_cbf_bytes(int32_t d, int32_t k);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           KmPrune2 *out);
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);

@@ -130,12 +130,19 @@ cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, c
 
 // ------------------------------------------------------------------ a4: finalize
 __global__ void __launch_bounds__(1024) km_finalize_kernel(const KmFinalizeArgs f) { km_finalize_block(f); }
+__global__ void __launch_bounds__(256) km_finalize_grid_kernel(const KmFinalizeArgs f) { km_finalize_grid(f); }
 
 cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t *launches) {
   int64_t kd = (int64_t)f.k * f.d;
-  int threads = kd >= 1024 ? 1024 : (int)(((kd + 31) / 32) * 32);
-  if (threads < 32) threads = 32;
-  km_finalize_kernel<<<1, threads, 0, s>>>(f);
+  if (kd > 16384) {   // large tables: spread the divisions over many blocks
+    int grid = (int)((kd + 256 * 4 - 1) / (256 * 4));
+    if (grid > 148) grid = 148;
+    km_finalize_grid_kernel<<<grid, 256, 0, s>>>(f);
+  } else {
+    int threads = kd >= 1024 ? 1024 : (int)(((kd + 31) / 32) * 32);
+    if (threads < 32) threads = 32;
+    km_finalize_kernel<<<1, threads, 0, s>>>(f);
+  }
   (*launches)++;
   return cudaGetLastError();
 }
