@@ -411,13 +411,25 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
     const int cpr = d >> 2, rpp = 32 / cpr, r_off = lane / cpr, q = lane - r_off * cpr;
     if (r_off >= rpp) return;
     const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
-    for (int r = warp * rpp + r_off; r < ROWS; r += (KB_THREADS / 32) * rpp) {
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (row0 + r < p.n) v = __ldg(reinterpret_cast<const float4 *>(p.x + (row0 + r) * (int64_t)d + e));
-      const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-      const int rr = r & (KT_M - 1);
-      unsigned char *dst = smem_raw + (r >> 7) * tile_bytes + kb * kb_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4) + within;
-      *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
+    const int rstep = (KB_THREADS / 32) * rpp;
+    // batches of 8 rows: all eight global loads are in flight before the first conversion
+    for (int r0 = warp * rpp + r_off; r0 < ROWS; r0 += 8 * rstep) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        const int r = r0 + u * rstep;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < ROWS && row0 + r < p.n) v[u] = __ldg(reinterpret_cast<const float4 *>(p.x + (row0 + r) * (int64_t)d + e));
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        const int r = r0 + u * rstep;
+        if (r >= ROWS) break;
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
+        const int rr = r & (KT_M - 1);
+        unsigned char *dst = smem_raw + (r >> 7) * tile_bytes + kb * kb_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4) + within;
+        *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
+      }
     }
   };
   auto load_b = [&](uint32_t sB, int64_t j0) {
@@ -499,6 +511,10 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
         load_a((ps + gridDim.x) * ROWS);
         load_b(sB0, 0);
         cp_async_commit();
+      } else if (t + 2 < ntiles) {
+        // B buffer b is free (MMA(t) has completed): tile t+2 streams in under epilogue(t)
+        load_b(b ? sB1 : sB0, (int64_t)(t + 2) * KT_N);
+        cp_async_commit();
       }
       const float *cnt_tile = cnb + b * KT_N;
       float *drow = dsm + row * 36;
@@ -535,11 +551,7 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
       }
       tc_fence_before();
       __syncthreads();
-      if (t + 2 < ntiles) {
-        load_b(b ? sB1 : sB0, (int64_t)(t + 2) * KT_N);
-        if (threadIdx.x < KT_N) cnb[b * KT_N + threadIdx.x] = p.cn[(t + 2) * KT_N + threadIdx.x];
-        cp_async_commit();
-      }
+      if (t + 2 < ntiles && threadIdx.x < KT_N) cnb[b * KT_N + threadIdx.x] = p.cn[(t + 2) * KT_N + threadIdx.x];
     }
     if (row0 + row < p.n) {
       int out[KT_CAND];
