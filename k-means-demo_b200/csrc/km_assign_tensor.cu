@@ -80,6 +80,24 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// issue only: the registers are valid after the next tmem_ld_wait()
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+// hits |= bit  iff  dist <= thr   (one compare + one predicated OR)
+__device__ __forceinline__ void kt_hit(unsigned &hits, float dist, float thr, unsigned bit) {
+  asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}" : "+r"(hits) : "f"(dist), "f"(thr), "r"(bit));
+}
 // 32 consecutive accumulator columns of this thread's TMEM lane
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -518,10 +536,9 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
       }
       const float *cnt_tile = cnb + b * KT_N;
       float *drow = dsm + row * 36;
-#pragma unroll 1
-      for (int c = 0; c < KT_N; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((mi * 2 + b) * KT_N + c), v);
+      const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((mi * 2 + b) * KT_N);
+      // one chunk of 32 columns: distances to shared memory, hit mask, then the rare hits
+      auto chunk = [&](const uint32_t (&v)[32], int c) {
         unsigned hits = 0;
 #pragma unroll
         for (int i4 = 0; i4 < 8; i4++) {
@@ -532,10 +549,10 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
           d4.z = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 2]), cn4.z);
           d4.w = fmaf(-2.0f, __uint_as_float(v[i4 * 4 + 3]), cn4.w);
           *reinterpret_cast<float4 *>(drow + i4 * 4) = d4;
-          if (d4.x <= thr) hits |= 1u << (i4 * 4 + 0);
-          if (d4.y <= thr) hits |= 1u << (i4 * 4 + 1);
-          if (d4.z <= thr) hits |= 1u << (i4 * 4 + 2);
-          if (d4.w <= thr) hits |= 1u << (i4 * 4 + 3);
+          kt_hit(hits, d4.x, thr, 1u << (i4 * 4 + 0));
+          kt_hit(hits, d4.y, thr, 1u << (i4 * 4 + 1));
+          kt_hit(hits, d4.z, thr, 1u << (i4 * 4 + 2));
+          kt_hit(hits, d4.w, thr, 1u << (i4 * 4 + 3));
         }
         while (hits) {
           const int i = __ffs(hits) - 1;
@@ -548,6 +565,22 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
             if (dist < runmin) { runmin = dist; thr = runmin + two_e; }
           }
         }
+      };
+      {
+        // the TMEM read of chunk c+1 is in flight while chunk c is processed
+        uint32_t va[32], vb[32];
+        tmem_ld32_issue(tcol + 0, va);
+        tmem_ld_wait();
+        tmem_ld32_issue(tcol + 32, vb);
+        chunk(va, 0);
+        tmem_ld_wait();
+        tmem_ld32_issue(tcol + 64, va);
+        chunk(vb, 32);
+        tmem_ld_wait();
+        tmem_ld32_issue(tcol + 96, vb);
+        chunk(va, 64);
+        tmem_ld_wait();
+        chunk(vb, 96);
       }
       tc_fence_before();
       __syncthreads();
