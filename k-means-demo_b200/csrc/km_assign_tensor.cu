@@ -359,7 +359,9 @@ __global__ void __launch_bounds__(KT_THREADS) km_tensor_coarse_kernel(const KmTe
         for (int a = 1; a < w; a++)        // insertion sort, ascending index (tie rule: lowest j first)
           for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
       }
-      *reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND) = make_int4(out[0], out[1], out[2], out[3]);
+      int4 *cdst = reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND);
+      cdst[0] = make_int4(out[0], out[1], out[2], out[3]);
+      cdst[1] = make_int4(out[4], out[5], out[6], out[7]);
     }
     __syncthreads();                       // lst is reused by the next point tile
   }
@@ -604,7 +606,9 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
         for (int a = 1; a < w; a++)
           for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
       }
-      *reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND) = make_int4(out[0], out[1], out[2], out[3]);
+      int4 *cdst = reinterpret_cast<int4 *>(p.cand + (row0 + row) * KT_CAND);
+      cdst[0] = make_int4(out[0], out[1], out[2], out[3]);
+      cdst[1] = make_int4(out[4], out[5], out[6], out[7]);
     }
     __syncthreads();
   }
@@ -668,25 +672,28 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
     const int64_t i = base + g;
     const bool live = i < n;
     const float *xr = x + (live ? i : 0) * (int64_t)d;
-    int4 cw = make_int4(-1, -1, -1, -1);
+    int4 cw = make_int4(-1, -1, -1, -1), cw2 = make_int4(-1, -1, -1, -1);
     int old = 0;
     float4 xq[4];
     if (live) {
       cw = *reinterpret_cast<const int4 *>(cand + i * KT_CAND);
+      cw2 = *reinterpret_cast<const int4 *>(cand + i * KT_CAND + 4);
       old = labels[i];
 #pragma unroll
       for (int q = 0; q < 4; q++)
         if (q < nq) xq[q] = *reinterpret_cast<const float4 *>(xr + (q * 8 + sl) * 4);
     }
     const bool scan_all = cw.x == -2;
-    const int ncand = !live ? 0 : scan_all ? k : ((cw.y < 0) ? 1 : (cw.z < 0) ? 2 : (cw.w < 0) ? 3 : 4);
+    const int ncand = !live ? 0 : scan_all ? k : ((cw.y < 0) ? 1 : (cw.z < 0) ? 2 : (cw.w < 0) ? 3 : (cw2.x < 0) ? 4 :
+                                                  (cw2.y < 0) ? 5 : (cw2.z < 0) ? 6 : (cw2.w < 0) ? 7 : 8);
+    auto pick = [&](int s) { return s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : s == 3 ? cw.w : s == 4 ? cw2.x : s == 5 ? cw2.y : s == 6 ? cw2.z : cw2.w; };
     // a lone survivor is the argmin by the coarse bound: no binary32 pass needed
     const int nloop = __reduce_max_sync(0xffffffffu, ncand > 1 ? ncand : 0);
     float b1 = __int_as_float(0x7f800000), b2 = b1;
     int i1 = scan_all ? 0 : cw.x;
     for (int s = 0; s < nloop; s++) {
       const bool act = ncand > 1 && s < ncand;
-      const int j = scan_all ? s : (s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : cw.w);
+      const int j = scan_all ? s : pick(s);
       float part = 0.f;
       if (act) {
         const float *cr = chi + (int64_t)j * d;
@@ -713,7 +720,7 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
         best = __longlong_as_double(0x7FF0000000000000LL);
         lab = 0;
         for (int s = 0; s < ncand; s++) {
-          const int j = scan_all ? s : (s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : cw.w);
+          const int j = scan_all ? s : pick(s);
           const double dj = km_dist2_f64(xr, c64 + (int64_t)j * d, d);
           if (dj < best) { best = dj; lab = j; }
         }

@@ -10,7 +10,7 @@
 
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
-#define KT_CAND 4      // tensor path: survivors listed per point
+#define KT_CAND 8      // tensor path: survivors listed per point (two int4)
 #define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
 
 struct km_ctx {
