@@ -200,6 +200,8 @@ KM_API km_status km_sync(km_ctx *ctx);
 /* with km_config.profile_kernels: summed device time of the assignment kernels launched
  * since the last reset (up to 256 are kept), and how many there were */
 KM_API km_status km_kernel_time(km_ctx *ctx, double *ms_sum, int32_t *launches, int32_t reset);
+/* switch km_config.profile_kernels on or off for the calls that follow */
+KM_API km_status km_set_profile(km_ctx *ctx, int32_t on);
 /* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
 KM_API int64_t km_launch_count(const km_ctx *ctx);
 

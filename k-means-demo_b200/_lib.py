@@ -69,6 +69,7 @@ PROTOTYPES = {
     "km_lloyd_step_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "km_sync": (_i32, [_vp]),
     "km_kernel_time": (_i32, [_vp, C.POINTER(_dbl), C.POINTER(_i32), _i32]),
+    "km_set_profile": (_i32, [_vp, _i32]),
     "km_launch_count": (_i64, [_vp]),
 }
 

@@ -199,6 +199,9 @@ class KMeansState:
         self._check(self._lib.km_kernel_time(self._h, C.byref(ms), C.byref(n), 1 if reset else 0))
         return ms.value, n.value
 
+    def set_profile(self, on):
+        self._check(self._lib.km_set_profile(self._h, 1 if on else 0))
+
     def launch_count(self):
         return int(self._lib.km_launch_count(self._h))
 

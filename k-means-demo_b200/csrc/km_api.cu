@@ -565,6 +565,12 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
     if (s != KM_OK) return s;
   }
   ctx->use_hilo = false;
+  {
+    // every centroid an update produces is a mean of points: max(max|x|, max|c0|) bounds max|c|
+    double cb = ctx->maxabs;
+    for (int64_t e = 0; e < (int64_t)k * d; e++) cb = std::max(cb, fabs(c_host[e]));
+    ctx->cbound = cb;
+  }
   if (ctx->p1) {
     // merge whatever pass is pending under the old centroids, then overwrite them
     km_status s = p1_flush(ctx, -1, -1);
@@ -662,6 +668,19 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.hilo = ctx->use_hilo ? 1 : 0;
   a.scale_a = ldexp(1.0, ctx->qa);
   a.scale_b = ldexp(1.0, ctx->QB);
+  {
+    // scales that depend on max|c| (same formulas as km_scales_from_cmax, from the host bound)
+    const double M = std::max(ctx->cbound, ctx->maxabs);
+    const int EM = M > 0.0 ? ilogb(M) + 1 : 0;
+    int dbits = 0;
+    while ((1 << dbits) <= ctx->d) dbits++;
+    a.h_cbound = M;
+    a.h_qi = ctx->QB - (2 * EM + 2 + dbits);
+    a.h_inertia_scale = ldexp(1.0, a.h_qi);
+    const double c2 = M * M;
+    a.h_tau_hilo = (float)(2.5 * (4.2 * ctx->d * 0x1.0p-72 * c2) + ctx->d * 0x1.0p-140) * 1.000001f;
+    a.h_tau_hi = (float)(2.5 * (1.01 * ctx->d * 0x1.0p-24 * c2) + ctx->d * 0x1.0p-140) * 1.000001f;
+  }
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
   a.t_cn = nullptr; a.t_cbf = nullptr; a.t_cand = nullptr; a.t_xnmax = 0.f;
@@ -1010,6 +1029,12 @@ extern "C" km_status km_kernel_time(km_ctx *ctx, double *ms_sum, int32_t *launch
   if (ms_sum) *ms_sum = sum;
   if (launches) *launches = ctx->prof_n;
   if (reset) ctx->prof_n = 0;
+  return KM_OK;
+}
+
+extern "C" km_status km_set_profile(km_ctx *ctx, int32_t on) {
+  KM_BIND(ctx);
+  ctx->cfg.profile_kernels = on ? 1 : 0;
   return KM_OK;
 }
 

@@ -80,6 +80,10 @@ struct KmSmallParams {
   float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
   int64_t chunk;       // points per block (multiple of 4)
+  double inertia_scale;  // 2^qi, from the host-side bound on max|c|
+  int qi;
+  float tau2;          // absolute error term of the filter for this instantiation (hi or hi/lo)
+  float cboundf;       // the bound on max|c| itself
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
   KmPrune2 pr;         // d == 2 candidate grid (used by the PRUNE instantiation)
 };
@@ -196,7 +200,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const bool pend = ps.D_in != nullptr;
   const long long changed_prev = pend ? ps.D_in[L.scal + KM_ACC_CHANGED] : 0;
   const bool upd = ps.apply_update && (!ps.needs_change || changed_prev > 0);
-  double cmax_in = 0.0, cmax_new = 0.0;
   for (int e = threadIdx.x; e < k * D; e += KM_SMALL_THREADS) {
     const int jj = e / D, t = e - jj * D;
     long long sa = ps.S_in[L.sa + e], sb = ps.S_in[L.sb + e], cn = ps.S_in[L.cnt + jj];
@@ -204,8 +207,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       const long long da = ps.D_in[L.sa + e], db = ps.D_in[L.sb + e], dc = ps.D_in[L.cnt + jj];
       if (ps.full_mode) { sa = da; sb = db; cn = dc; } else { sa += da; sb += db; cn += dc; }
     }
-    const double cin = ps.C_in[e];
-    double c = cin;
+    double c = ps.C_in[e];
     if (upd && cn > 0) c = __ddiv_rn(km_fixed_to_double(sa, sb, ps.QB, ps.qa + ps.QB), (double)cn);
     const float h = __double2float_rn(c);
     ncf[jj * CROW + t] = -h;
@@ -217,46 +219,23 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       if (t == 0) ps.S_out[L.cnt + jj] = cn;
       ps.C_out[e] = c;
     }
-    cmax_in = fmax(cmax_in, fabs(cin));
-    cmax_new = fmax(cmax_new, fabs(c));
   }
-  __shared__ double s_red[2][KM_SMALL_THREADS / 32];
-  __shared__ double s_iscale;
-  __shared__ float s_tau, s_cmaxf;
   __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, inertia limbs, rescored
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int red_warps = min(KM_SMALL_THREADS / 32, (k * D + 31) / 32);   // warps that saw an element
-  if (warp < red_warps) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      cmax_in = fmax(cmax_in, __shfl_xor_sync(0xffffffffu, cmax_in, o));
-      cmax_new = fmax(cmax_new, __shfl_xor_sync(0xffffffffu, cmax_new, o));
-    }
-    if (lane == 0) { s_red[0][warp] = cmax_in; s_red[1][warp] = cmax_new; }
-  }
+  const int lane = threadIdx.x & 31;
   if (threadIdx.x < KM_ACC_SCALARS) s_scal[threadIdx.x] = 0;
   KmBlockTab T;
   T.L = L;
   T.tab = p.tab_in_smem ? stab : ps.D_out;
   if (p.tab_in_smem) km_tab_zero(stab, L.scal);
-  if (blockIdx.x == 0 && ps.D_zero)
-    for (int e = threadIdx.x; e < (int)L.len; e += KM_SMALL_THREADS) ps.D_zero[e] = 0;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double mi = 0.0, mn = 0.0;
-    for (int w = 0; w < red_warps; w++) { mi = fmax(mi, s_red[0][w]); mn = fmax(mn, s_red[1][w]); }
-    const KmScales sc = km_scales_from_cmax(mn, ps.maxabs_x, D, ps.QB);
-    s_iscale = sc.inertia_scale;
-    s_tau = HILO ? sc.tau_hilo : sc.tau_hi;
-    s_cmaxf = __double2float_ru(mn);
-    if (blockIdx.x == 0 && pend && ps.slot) {
-      // the pending pass ran under the scales of C_in
-      const KmScales si = km_scales_from_cmax(mi, ps.maxabs_x, D, ps.QB);
+  if (blockIdx.x == 0) {
+    if (ps.D_zero)
+      for (int e = threadIdx.x; e < (int)L.len; e += KM_SMALL_THREADS) ps.D_zero[e] = 0;
+    if (threadIdx.x == 0 && pend && ps.slot) {
       KmStatSlot sl;
       sl.it = ps.it_pending;
       sl.changed = changed_prev;
       sl.inertia = km_fixed_to_double(ps.D_in[L.scal + KM_ACC_INERTIA_A], ps.D_in[L.scal + KM_ACC_INERTIA_B], ps.QB,
-                                      si.qi + ps.QB);
+                                      p.qi + ps.QB);
       sl.rescored = ps.D_in[L.scal + KM_ACC_RESCORED];
       sl.updated = upd ? 1 : 0;
       sl.pad = 0;
@@ -264,8 +243,11 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     }
   }
   __syncthreads();
-  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = s_iscale;
-  const float tau2 = s_tau;   // absolute part of the ambiguity threshold (2.5x margin included)
+  // The error term of the filter and the inertia scale need max|c|.  Every centroid the
+  // update produces is a mean of points, so max(max|x|, max|c0|) — known on the host when the
+  // centroids were set — bounds it for every later pass: no reduction, no second barrier.
+  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = p.inertia_scale;
+  const float tau2 = p.tau2;   // absolute part of the ambiguity threshold (2.5x margin included)
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
 
@@ -279,7 +261,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     // geometry; `margin` (1e-5 of the squared coordinate scale, ~7x the binary32 error of
     // the expressions below incl. the rounding of m) only ever keeps extra candidates.
     const KmPrune2 &pr = p.pr;
-    const float M = s_cmaxf + pr.absmax;
+    const float M = p.cboundf + pr.absmax;
     const float margin = 1e-5f * M * M;
     const float hx = pr.inv_sx, hy = pr.inv_sy;
     for (int cell = threadIdx.x; cell < pr.gp * pr.gp; cell += KM_SMALL_THREADS) {
@@ -587,6 +569,10 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   p.chunk = chunk;
   p.scale_a = a.scale_a;
   p.scale_b = a.scale_b;
+  p.inertia_scale = a.h_inertia_scale;
+  p.qi = a.h_qi;
+  p.tau2 = HILO ? a.h_tau_hilo : a.h_tau_hi;
+  p.cboundf = (float)a.h_cbound * 1.0000002f;
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
   (*launches)++;
   return cudaGetLastError();

@@ -58,6 +58,7 @@ struct km_ctx {
   int32_t host_it = 0;              // assign steps issued since the last label reset
   int32_t last_path = 0;
   int32_t QB = 0, qa = 0, E = 0, NB = 0;
+  double cbound = 0.0;              // max(max|x|, max|c0|): bounds max|c| for every pass until centroids are set again
   bool use_hilo = false;            // small-d filter escalated to hi/lo centroid pairs
   bool labels_fresh = true;         // labels == -1 everywhere, sums zero
 
@@ -107,6 +108,9 @@ struct KmAssignArgs {
   int sm_count;
   int max_smem_optin;
   double scale_a, scale_b;  // 2^qa, 2^QB (host copies of KmState's)
+  double h_cbound, h_inertia_scale;  // small-d path: host-side bound on max|c| and the scales derived from it
+  int h_qi;
+  float h_tau_hilo, h_tau_hi;
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
   float *t_cn;         // tensor path: |chi_j|^2 (padded)
