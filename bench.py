@@ -232,12 +232,21 @@ def run_ours(args, wl):
     # keep the GPU loaded long enough for nvidia-smi to see the clocks this workload runs at
     t_load0 = time.time()
     t_end = time.perf_counter() + args.burn
-    while time.perf_counter() < t_end:
+    while True:
+        # every rank must issue the same number of steps (each step is a collective): rank 0's
+        # clock decides, the others follow
+        go = time.perf_counter() < t_end
+        if world > 1:
+            flag = torch.tensor([1 if go else 0], dtype=torch.int32, device=dev)
+            dist.broadcast(flag, 0)
+            go = bool(flag.item())
+        if not go:
+            break
         for _ in range(20):
-            flush.zero_()
+            if not args.no_flush:
+                flush.zero_()
             st.step_async()
         torch.cuda.synchronize()
-    # back to the seeded start: timed steps are Lloyd iterations W+1 .. W+K of a real run
     def timed_pass(profile):
         """Lloyd iterations W+1..W+K from the seeded init; per-step CUDA events, L2 flushed between steps."""
         st.set_profile(profile)
