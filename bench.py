@@ -4,10 +4,13 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c4|c5]
 
 A "step" is one Lloyd iteration (assignment fused with the partial sums, then the
-centroid update) over this rank's shard of seeded synthetic blobs.  Default workload
-is BASELINE.json configs[1] (N=1e6, d=2, k=8 on one B200); under torchrun every rank
-holds one such shard (weak scaling) and the step gains one NCCL all-reduce of the packed
-order-free sums.  One JSON line on stdout (rank 0); see DESIGN.md §7 for every field.
+centroid update) over this rank's shard of seeded synthetic blobs.  Default workload is the
+one BASELINE.json's metric ("... at 1/2/4/8 B200 ...") is quoted on across 1..8 GPUs:
+configs[4] (N=1e9, d=2, k=64 over 8 B200) in its per-GPU form — every rank holds one shard of
+1.25e8 points (weak scaling; --gpus 8 is exactly configs[4], and one shard fits one GPU) and a
+step carries one NCCL all-reduce of the packed order-free sums.  `--workload c2` runs
+configs[1] (N=1e6, d=2, k=8 per GPU), `c3`/`c4` the tensor-path shapes.  One JSON line on
+stdout (rank 0); see DESIGN.md §7 for every field.
 
 `--impl reference` times the CPU restatement of the path (oracle/, all host threads) on the
 same workload: the reference itself has no Lloyd code and no JS engine exists on this image
@@ -393,7 +396,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c5")
     ap.add_argument("--burn", type=float, default=1.5, help="seconds of untimed load before the timed steps (clock sampling)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--run-iters", type=int, default=50)
