@@ -94,6 +94,8 @@ static km_status bind(km_ctx *ctx) {
 static void free_points(km_ctx *ctx) {
   if (ctx->x && ctx->own_x) cudaFree(ctx->x);
   if (ctx->labels) cudaFree(ctx->labels);
+  if (ctx->perm) cudaFree(ctx->perm);
+  ctx->perm = nullptr; ctx->passes_since_upload = 0;
   if (ctx->t_cand) cudaFree(ctx->t_cand);
   ctx->t_cand = nullptr; ctx->t_cand_n = 0;
   ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
@@ -320,6 +322,8 @@ static km_status alloc_points(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype, 
   // step must not pay cudaMalloc/cudaFree)
   if (alloc_x && ctx->own_x && ctx->x && ctx->labels && ctx->n == n && ctx->d == d && ctx->dtype == dtype) {
     ctx->have_points = false;
+    if (ctx->perm) cudaFree(ctx->perm);   // new rows arrive in the caller's order
+    ctx->perm = nullptr; ctx->passes_since_upload = 0;
     return KM_OK;
   }
   free_points(ctx);
@@ -511,6 +515,16 @@ extern "C" km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t 
   if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
   if (i0 < 0 || n < 0 || i0 + n > ctx->n || (n > 0 && !host)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_points: range outside the shard");
   size_t row = (size_t)ctx->d * elt_size(ctx->dtype);
+  if (ctx->perm && n > 0) {  // stored in cell order: put the requested rows back in the caller's
+    float *tmp = nullptr;
+    KM_CUDA(ctx, cudaMalloc(&tmp, (size_t)n * row));
+    cudaError_t e = km_unpermute_rows2((const float *)ctx->x, ctx->perm, ctx->n, i0, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches);
+    km_status s = KM_OK;
+    if (e == cudaSuccess) s = copy_d2h(ctx, host, tmp, (size_t)n * row);
+    cudaFree(tmp);
+    KM_CUDA(ctx, e);
+    return s;
+  }
   return copy_d2h(ctx, host, (const char *)ctx->x + (size_t)i0 * row, (size_t)n * row);
 }
 
@@ -629,8 +643,13 @@ extern "C" km_status km_init_forgy(km_ctx *ctx, int32_t k, uint64_t seed) {
   for (int32_t s = 0; s < k; s++) {
     int64_t g = idx[s];
     if (g < ctx->i0 || g >= ctx->i0 + ctx->n) continue;  // another rank owns this row
-    KM_CUDA(ctx, cudaMemcpyAsync(tmp.data(), (const char *)ctx->x + (size_t)(g - ctx->i0) * row, row, cudaMemcpyDeviceToHost, ctx->stream));
-    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->perm) {
+      km_status gs = km_get_points(ctx, tmp.data(), g - ctx->i0, 1);
+      if (gs != KM_OK) return gs;
+    } else {
+      KM_CUDA(ctx, cudaMemcpyAsync(tmp.data(), (const char *)ctx->x + (size_t)(g - ctx->i0) * row, row, cudaMemcpyDeviceToHost, ctx->stream));
+      KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     for (int32_t t = 0; t < d; t++)
       c[(size_t)s * d + t] = ctx->dtype == KM_DTYPE_F32 ? (double)((const float *)tmp.data())[t] : ((const double *)tmp.data())[t];
   }
@@ -688,6 +707,26 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
     a.prune = 1;
+  a.sorted = (a.prune && ctx->perm && memcmp(&a.pr, &ctx->sort_pr, sizeof(KmPrune2)) == 0) ? 1 : 0;
+}
+
+// Store layout for the pruned d = 2 path: once a job has shown it iterates (third pass on the
+// same upload, or km_run asked for >= 3), reorder the owned points by candidate-grid cell so
+// a warp's points share their candidates (km_sort.cu).  Results do not depend on the order.
+static km_status maybe_sort_points(km_ctx *ctx) {
+  if (ctx->perm || !ctx->own_x || ctx->d != 2 || ctx->dtype != KM_DTYPE_F32 || !ctx->have_bbox || ctx->cfg.no_prune ||
+      ctx->passes_since_upload < 2 || !ctx->p1)
+    return KM_OK;
+  static const bool off = getenv("KM_NO_SORT") != nullptr;
+  if (off) return KM_OK;
+  KmPrune2 pr;
+  memset(&pr, 0, sizeof(pr));
+  if (!km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &pr)) return KM_OK;
+  float *x = (float *)ctx->x;
+  KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
+  ctx->x = x;
+  ctx->sort_pr = pr;
+  return KM_OK;
 }
 
 // ---- general path: assignment kernel, [NCCL all-reduce of the packed table], finalize kernel
@@ -780,7 +819,10 @@ static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
 
 // an assignment pass; the pass pending before it is merged with the intent it was issued with
 static km_status p1_assign(km_ctx *ctx, int intent_update, int intent_nc) {
-  km_status s = p1_launch(ctx, true, ctx->p1_pending ? ctx->p1_pend_update : 0, ctx->p1_pending ? ctx->p1_pend_nc : 0);
+  km_status s = maybe_sort_points(ctx);
+  if (s != KM_OK) return s;
+  ctx->passes_since_upload++;
+  s = p1_launch(ctx, true, ctx->p1_pending ? ctx->p1_pend_update : 0, ctx->p1_pending ? ctx->p1_pend_nc : 0);
   ctx->p1_pend_update = intent_update;
   ctx->p1_pend_nc = intent_nc;
   return s;
@@ -912,6 +954,8 @@ extern "C" km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats) {
   if (s != KM_OK) return s;
   if (max_iter < 1) return fail(ctx, KM_ERR_INVALID_ARG, "km_run: max_iter must be >= 1");
   if ((s = reset_labels(ctx)) != KM_OK) return s;
+  if (max_iter >= 3 && ctx->passes_since_upload < 2) ctx->passes_since_upload = 2;  // an iterating job: lay the store out for it now
+  if ((s = maybe_sort_points(ctx)) != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   int32_t issued = 0, checked = 0;
   KmStatSlot last;
@@ -951,6 +995,16 @@ extern "C" km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n) {
   KM_BIND(ctx);
   if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
   if (n != ctx->n || (n > 0 && !out)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_labels: n must equal the shard size");
+  if (ctx->perm && n > 0) {
+    int32_t *tmp = nullptr;
+    KM_CUDA(ctx, cudaMalloc(&tmp, (size_t)n * sizeof(int32_t)));
+    cudaError_t e = km_unpermute_labels(ctx->labels, ctx->perm, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches);
+    km_status s = KM_OK;
+    if (e == cudaSuccess) s = copy_d2h(ctx, out, tmp, (size_t)n * sizeof(int32_t));
+    cudaFree(tmp);
+    KM_CUDA(ctx, e);
+    return s;
+  }
   return copy_d2h(ctx, out, ctx->labels, (size_t)n * sizeof(int32_t));
 }
 

@@ -79,13 +79,15 @@ struct KmSmallParams {
   unsigned key_mask;   // low bits of the distance key that hold the centroid index
   float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
-  int64_t chunk;       // points per block (multiple of 4)
+  int64_t chunk;       // points per chunk (multiple of 4); block b walks chunks b, b + grid, ...
+  int64_t nchunks;
   double inertia_scale;  // 2^qi, from the host-side bound on max|c|
   int qi;
   float tau2;          // absolute error term of the filter for this instantiation (hi or hi/lo)
   float cboundf;       // the bound on max|c| itself
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
   KmPrune2 pr;         // d == 2 candidate grid (used by the PRUNE instantiation)
+  int sorted;          // PRUNE: the points are stored in ascending cell order of exactly this grid
 };
 
 // What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
@@ -181,15 +183,24 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 
   // this block's contiguous chunk of points, walked in rounds of THREADS*PPT; everything
   // inside the chunk is addressed with 32-bit offsets from the chunk's base
-  const int64_t c0 = (int64_t)blockIdx.x * p.chunk;
-  const int cn = (int)max((int64_t)0, min(p.n - c0, p.chunk));
-  const float *__restrict__ xb = p.x + c0 * D;
-  int32_t *__restrict__ lb = p.labels + c0;
   constexpr int per_round = KM_SMALL_THREADS * PPT;
+  auto chunk_len = [&](int64_t c) { return (int)max((int64_t)0, min(p.n - c * p.chunk, p.chunk)); };
+  // the two ends of a chunk of cell-sorted points give the cells it touches
+  auto chunk_ends = [&](int64_t c, float2 &first, float2 &last) {
+    const int len = chunk_len(c);
+    if (len > 0) {
+      const float2 *xc = reinterpret_cast<const float2 *>(p.x) + c * p.chunk;
+      first = __ldg(xc);
+      last = __ldg(xc + (len - 1));
+    }
+  };
 
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
-  km_load_batch<D>(cur, xb, lb, 0, cn);
+  float2 end_a = make_float2(0.f, 0.f), end_z = make_float2(0.f, 0.f);
+  km_load_batch<D>(cur, p.x + (int64_t)blockIdx.x * p.chunk * D, p.labels + (int64_t)blockIdx.x * p.chunk, 0,
+                   chunk_len(blockIdx.x));
+  if (PRUNE && p.sorted) chunk_ends(blockIdx.x, end_a, end_z);
 
   // ---- prologue = the previous pass's centroid update (a4), redone by every block:
   //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
@@ -251,18 +262,24 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
 
-  if constexpr (PRUNE) {
-    // Candidate list of a cell (a box with centre m and half sides hx/2, hy/2).  Let b be the
-    // centroid nearest to m.  For any other centroid j,
-    //     f_j(x) = |x - c_j|^2 - |x - c_b|^2 = a . x + const,   a = -2 (c_j - c_b)
-    // is LINEAR in x, so its minimum over the box is f_j(m) - (|a_x| hx + |a_y| hy) / 2.  If that
-    // minimum is positive, b beats j at every point of the box and j can neither win nor tie
-    // there: j is dropped.  Everything else (b included) is a candidate.  The test is exact
-    // geometry; `margin` (1e-5 of the squared coordinate scale, ~7x the binary32 error of
-    // the expressions below incl. the rounding of m) only ever keeps extra candidates.
+  int cell_lo_b = 0, cell_hi_b = 0;   // PRUNE + sorted: the cell range built for the current chunk
+  // Candidate list of a cell (a box with centre m and half sides hx/2, hy/2).  Let b be the
+  // centroid nearest to m.  For any other centroid j,
+  //     f_j(x) = |x - c_j|^2 - |x - c_b|^2 = a . x + const,   a = -2 (c_j - c_b)
+  // is LINEAR in x, so its minimum over the box is f_j(m) - (|a_x| hx + |a_y| hy) / 2.  If that
+  // minimum is positive, b beats j at every point of the box and j can neither win nor tie
+  // there: j is dropped.  Everything else (b included) is a candidate.  The test is exact
+  // geometry; `margin` (1e-5 of the squared coordinate scale, ~7x the binary32 error of
+  // the expressions below incl. the rounding of m) only ever keeps extra candidates.
+  const float prune_M = p.cboundf + p.pr.absmax;
+  const float margin = 1e-5f * prune_M * prune_M;
+  auto cell_of = [&](float2 v) {
+    return min(__float_as_int(fmaf(v.y, p.pr.sy, p.pr.kym)) & 0x3FFFFF, p.pr.gp - 1) * p.pr.gp +
+           min(__float_as_int(fmaf(v.x, p.pr.sx, p.pr.kxm)) & 0x3FFFFF, p.pr.gp - 1);
+  };
+  // one thread per cell: for building the whole grid (points in the caller's order)
+  auto build_cells_all = [&]() {
     const KmPrune2 &pr = p.pr;
-    const float M = p.cboundf + pr.absmax;
-    const float margin = 1e-5f * M * M;
     const float hx = pr.inv_sx, hy = pr.inv_sy;
     for (int cell = threadIdx.x; cell < pr.gp * pr.gp; cell += KM_SMALL_THREADS) {
       const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
@@ -288,28 +305,102 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       }
       cells[cell] = word | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
     }
-    __syncthreads();
+  };
+  // one warp per cell, lanes over the centroids: for the few cells one chunk of cell-sorted
+  // points touches.  Same arithmetic, same words as build_cells_all.
+  auto build_cells_range = [&](int lo, int hi) {
+    const KmPrune2 &pr = p.pr;
+    const float hx = pr.inv_sx, hy = pr.inv_sy;
+    for (int cell = lo + (int)(threadIdx.x >> 5); cell <= hi; cell += KM_SMALL_THREADS / 32) {
+      const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
+      const float mx = ((float)ix - pr.kx) * pr.inv_sx, my = ((float)iy - pr.ky) * pr.inv_sy;
+      unsigned long long bestkey = ~0ULL;   // (distance bits, index): min = nearest, lowest index on ties
+      for (int j = lane; j < k; j += 32) {
+        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
+        const unsigned long long key = ((unsigned long long)__float_as_uint(fmaf(dx, dx, dy * dy)) << 32) | (unsigned)j;
+        bestkey = min(bestkey, key);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) bestkey = min(bestkey, __shfl_xor_sync(0xffffffffu, bestkey, o));
+      const int bj = (int)(bestkey & 0xFFFFFFFFu);
+      const float dbest = __uint_as_float((unsigned)(bestkey >> 32));
+      const float bx = ncf[bj * CROW], by = ncf[bj * CROW + 1];
+      unsigned wlo = 0, whi = 0;
+      int cnt = 0;
+      for (int j0 = 0; j0 < k; j0 += 32) {
+        const int j = j0 + lane;
+        bool keep = false;
+        if (j < k) {
+          const float ncx = ncf[j * CROW], ncy = ncf[j * CROW + 1];
+          const float dx = mx + ncx, dy = my + ncy;
+          const float fm = fmaf(dx, dx, dy * dy) - dbest;
+          const float swing = fabsf(ncx - bx) * hx + fabsf(ncy - by) * hy;
+          keep = fm - swing <= margin;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+          const int rank = cnt + __popc(bal & ((1u << lane) - 1u));
+          if (rank < KM_PRUNE_CAP) {
+            const unsigned long long w = (unsigned long long)j << (8 * (rank + 1));
+            wlo |= (unsigned)w;
+            whi |= (unsigned)(w >> 32);
+          }
+        }
+        cnt += __popc(bal);
+      }
+      wlo = __reduce_or_sync(0xffffffffu, wlo);
+      whi = __reduce_or_sync(0xffffffffu, whi);
+      if (lane == 0)
+        cells[cell] = ((unsigned long long)whi << 32) | wlo | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
+    }
+  };
+  if constexpr (PRUNE) {
+    if (!p.sorted) {
+      build_cells_all();
+      __syncthreads();
+    }
   }
 
   int changed = 0, rescored = 0;
   double inertia = 0.0;
 
+  for (int64_t ch = blockIdx.x; ch < p.nchunks; ch += gridDim.x) {
+  const int cn = chunk_len(ch);
+  const float *__restrict__ xb = p.x + ch * p.chunk * D;
+  int32_t *__restrict__ lb = p.labels + ch * p.chunk;
+  const int64_t ch_next = ch + gridDim.x;
+  if constexpr (PRUNE) {
+    if (p.sorted) {
+      // candidate words for the cells between this chunk's first and last point
+      if (ch != (int64_t)blockIdx.x) __syncthreads();   // the previous chunk's readers are done
+      cell_lo_b = cell_of(end_a);
+      cell_hi_b = max(cell_of(end_z), cell_lo_b);
+      build_cells_range(cell_lo_b, cell_hi_b);
+      __syncthreads();
+    }
+  }
   for (int r0 = 0; r0 < cn; r0 += per_round) {
-    // software pipeline: the next round's loads are in flight during this round's arithmetic
+    // software pipeline: the next round's loads (the next chunk's first, at the end of this
+    // one) are in flight during this round's arithmetic
     KmBatch<D> nxt;
-    if (r0 + per_round < cn) km_load_batch<D>(nxt, xb, lb, r0 + per_round, cn);
+    if (r0 + per_round < cn) {
+      km_load_batch<D>(nxt, xb, lb, r0 + per_round, cn);
+    } else if (ch_next < p.nchunks) {
+      km_load_batch<D>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
+      if (PRUNE && p.sorted) chunk_ends(ch_next, end_a, end_z);
+    }
 
     // ---- binary32 filter, top-2 on integer keys
     unsigned m1[PPT], m2[PPT];
 #pragma unroll
     for (int q = 0; q < PPT; q++) { m1[q] = 0xFFFFFFFFu; m2[q] = 0xFFFFFFFFu; }
+    bool one_candidate = false;   // warp-uniform: every point of the round has the same single candidate
 
     if constexpr (PRUNE) {
       // each point looks only at its cell's candidates; a cell that overflowed its word
       // (count byte 0xFF) sends its points to the binary64 scan of all k below
       const KmPrune2 &pr = p.pr;
       unsigned long long w[PPT];
-      int nn[PPT], nmax = 0;
 #pragma unroll
       for (int q = 0; q < PPT; q++) {
         float x0, x1;
@@ -318,26 +409,67 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         // the end of a ragged round (a negative index shows up as a huge masked value)
         const int ix = min(__float_as_int(fmaf(x0, pr.sx, pr.kxm)) & 0x3FFFFF, pr.gp - 1);
         const int iy = min(__float_as_int(fmaf(x1, pr.sy, pr.kym)) & 0x3FFFFF, pr.gp - 1);
-        w[q] = cells[iy * pr.gp + ix];
-        nn[q] = (int)(w[q] & 0xFF);
-        if (nn[q] == 0xFF) nn[q] = 0;   // overflow: leave m1 = m2 = max -> "ambiguous" -> full scan
-        nmax = max(nmax, nn[q]);
+        int cell = iy * pr.gp + ix;
+        if (p.sorted) cell = min(max(cell, cell_lo_b), cell_hi_b);   // dead lanes only: stay inside what was built
+        w[q] = cells[cell];
       }
+      // Do all 32 x PPT points of the warp share one candidate word?  With the points stored in
+      // cell order nearly every warp does: the candidates are then warp-uniform (one broadcast
+      // LDS each, no predication), and a single-candidate word needs no filter at all.
+      const unsigned long long w0 = __shfl_sync(0xffffffffu, w[0], 0);
+      bool same = true;
 #pragma unroll
-      for (int c = 0; c < KM_PRUNE_CAP; c++) {
-        if (c >= nmax) break;
+      for (int q = 0; q < PPT; q++) same &= (w[q] == w0);
+      const int n0 = (int)(w0 & 0xFF);
+      if (__all_sync(0xffffffffu, same) && n0 != 0xFF) {
+        if (n0 == 1 && p.exact_inertia) {
+          // the only candidate wins: key = its index under distance bits 0 ("clear" below)
+#pragma unroll
+          for (int q = 0; q < PPT; q++) m1[q] = (unsigned)((w0 >> 8) & 0xFF);
+          one_candidate = true;
+        } else {
+          for (int c = 0; c < n0; c++) {
+            const int j = (int)((w0 >> (8 * (c + 1))) & 0xFF);
+            const float *crow = ncf + j * CROW;
+            const f32x2 nh = *reinterpret_cast<const f32x2 *>(crow);
+            f32x2 nl = 0;
+            if (HILO) nl = *reinterpret_cast<const f32x2 *>(crow + 2);
+#pragma unroll
+            for (int q = 0; q < PPT; q++) {
+              f32x2 df = add2(cur.xq[q][0], nh);
+              if (HILO) df = add2(df, nl);
+              float lo, hi;
+              unpk2(mul2(df, df), lo, hi);
+              const unsigned key = (__float_as_uint(lo + hi) & ~mask) | (unsigned)j;
+              m2[q] = min(m2[q], max(m1[q], key));
+              m1[q] = min(m1[q], key);
+            }
+          }
+        }
+      } else {
+        int nn[PPT], nmax = 0;
 #pragma unroll
         for (int q = 0; q < PPT; q++) {
-          if (c < nn[q]) {
-            const int j = (int)((w[q] >> (8 * (c + 1))) & 0xFF);
-            const float *crow = ncf + j * CROW;
-            f32x2 df = add2(cur.xq[q][0], *reinterpret_cast<const f32x2 *>(crow));
-            if (HILO) df = add2(df, *reinterpret_cast<const f32x2 *>(crow + 2));
-            float lo, hi;
-            unpk2(mul2(df, df), lo, hi);
-            const unsigned key = (__float_as_uint(lo + hi) & ~mask) | (unsigned)j;
-            m2[q] = min(m2[q], max(m1[q], key));
-            m1[q] = min(m1[q], key);
+          nn[q] = (int)(w[q] & 0xFF);
+          if (nn[q] == 0xFF) nn[q] = 0;   // overflow: leave m1 = m2 = max -> "ambiguous" -> full scan
+          nmax = max(nmax, nn[q]);
+        }
+#pragma unroll
+        for (int c = 0; c < KM_PRUNE_CAP; c++) {
+          if (c >= nmax) break;
+#pragma unroll
+          for (int q = 0; q < PPT; q++) {
+            if (c < nn[q]) {
+              const int j = (int)((w[q] >> (8 * (c + 1))) & 0xFF);
+              const float *crow = ncf + j * CROW;
+              f32x2 df = add2(cur.xq[q][0], *reinterpret_cast<const f32x2 *>(crow));
+              if (HILO) df = add2(df, *reinterpret_cast<const f32x2 *>(crow + 2));
+              float lo, hi;
+              unpk2(mul2(df, df), lo, hi);
+              const unsigned key = (__float_as_uint(lo + hi) & ~mask) | (unsigned)j;
+              m2[q] = min(m2[q], max(m1[q], key));
+              m1[q] = min(m1[q], key);
+            }
           }
         }
       }
@@ -396,43 +528,75 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     auto tail = [&](auto full_tag) {
       constexpr bool FULL = decltype(full_tag)::value;
       int newlab[PPT];
+      bool anypush = false;
+      if (PRUNE && FULL && one_candidate) {
+        // whole warp, one candidate: nothing to compare — the winner's exact distance for the
+        // inertia, and a look at the old labels
+        const int lab = (int)m1[0];
+        const double c0 = cd[(size_t)lab * D], c1 = cd[(size_t)lab * D + (D > 1 ? 1 : 0)];
+#pragma unroll
+        for (int q = 0; q < PPT; q++) {
+          float x0, x1;
+          unpk2(cur.xq[q][0], x0, x1);
+          const double d0 = __dsub_rn((double)x0, c0), d1 = __dsub_rn((double)x1, c1);
+          inertia += __dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1));   // 0 + a + b == a + b exactly
+          newlab[q] = lab;
+          const bool moved = lab != cur.old[q];
+          changed += moved ? 1 : 0;
+          anypush |= p.incremental ? moved : true;
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < PPT; q++) {
+          bool live = true;
+          if (!FULL) live = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV) < cn;
+          int lab = (int)(m1[q] & mask);
+          float xr[D];
+#pragma unroll
+          for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
+          if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
+          const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
+          // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score.
+          // No runner-up at all (k == 1, or a pruned cell with a single candidate) is unambiguous
+          // by construction; no winner at all (an overflowed cell) is not.
+          const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
+          double best;
+          if (live && !clear) {
+            rescored++;
+            best = __longlong_as_double(0x7FF0000000000000LL);
+            lab = 0;
+            for (int j = 0; j < k; j++) {
+              const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
+              if (dj < best) { best = dj; lab = j; }
+            }
+          } else {
+            best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
+          }
+          if (!live) { best = 0.0; lab = cur.old[q]; }
+          inertia += best;
+          newlab[q] = lab;
+          const bool moved = lab != cur.old[q];
+          changed += moved ? 1 : 0;
+          anypush |= live && (p.incremental ? moved : true);
+        }
+      }
+      // ---- commit.  Most rounds of a converging run re-label nobody: one vote settles that.
+      if (!__any_sync(0xffffffffu, anypush)) return;
 #pragma unroll
       for (int q = 0; q < PPT; q++) {
         bool live = true;
         if (!FULL) live = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV) < cn;
-        int lab = (int)(m1[q] & mask);
-        float xr[D];
-#pragma unroll
-        for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
-        if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
-        const float b1 = __uint_as_float(m1[q] & ~mask), b2 = __uint_as_float(m2[q] & ~mask);
-        // unambiguous iff the gap clears the error bound; NaN/Inf fall through to the re-score.
-        // No runner-up at all (k == 1, or a pruned cell with a single candidate) is unambiguous
-        // by construction; no winner at all (an overflowed cell) is not.
-        const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
-        double best;
-        if (live && !clear) {
-          rescored++;
-          best = __longlong_as_double(0x7FF0000000000000LL);
-          lab = 0;
-          for (int j = 0; j < k; j++) {
-            const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
-            if (dj < best) { best = dj; lab = j; }
-          }
-        } else {
-          best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
-        }
-        if (!live) { best = 0.0; lab = cur.old[q]; }
-        inertia += best;
-        newlab[q] = lab;
-        const bool moved = lab != cur.old[q];
-        changed += moved ? 1 : 0;
+        const int lab = newlab[q];
         // queue the move (incremental: re-labelled points only; full: every live point)
-        const bool push = live && (p.incremental ? moved : true);
+        const bool push = live && (p.incremental ? (lab != cur.old[q]) : true);
         const unsigned bal = __ballot_sync(0xffffffffu, push);
         if (bal) {
           if (push) {
             unsigned *e = qbuf + ((q_head + q_count + __popc(bal & ((1u << lane) - 1u))) & (QCAP - 1)) * QW;
+            float xr[D];
+#pragma unroll
+            for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], xr[2 * m], xr[2 * m + 1]);
+            if (D == 1 || TAIL) xr[D - 1] = cur.xs[q];
 #pragma unroll
             for (int t = 0; t < D; t++) e[t] = __float_as_uint(xr[t]);
             e[D] = (unsigned)(p.incremental ? cur.old[q] : -1);
@@ -477,6 +641,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     };
     if (r0 + per_round <= cn) tail(std::true_type{}); else tail(std::false_type{});
     cur = nxt;
+  }
   }
 
   // whatever is still queued (fewer than 32 entries per warp)
@@ -540,8 +705,10 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   p.key_mask = (1u << bits) - 1u;
   // (D+6) u for the arithmetic, 2^-(23-bits) for the key truncation, x2.5 margin
   p.rho2 = 2.5f * ((float)(D + 6) * 0x1.0p-24f + ldexpf(1.0f, bits - 23));
+  p.sorted = 0;
   if (PRUNE) {
     p.pr = a.pr;
+    p.sorted = a.sorted;
     smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);
   }
   smem += (size_t)(KM_SMALL_THREADS / 32) * 64 * (D + 2) * sizeof(unsigned);   // per-warp move queues
@@ -565,8 +732,19 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   if (chunk > max_chunk) chunk = max_chunk & ~(int64_t)3;
   grid64 = (a.n + chunk - 1) / chunk;
   if (grid64 < 1) grid64 = 1;   // n == 0: one block still runs the prologue (publish / update)
-  const int grid = (int)grid64;
+  int grid = (int)grid64;
   p.chunk = chunk;
+  p.nchunks = grid64;
+  if (PRUNE && p.sorted && a.n >= cap * per_round * 8) {
+    // Cell-sorted points: how many candidates a point has depends on where it lies, so equal
+    // contiguous shares are not equal work.  Cut the shard into ~32 chunks per block (whole
+    // rounds each) and deal them round-robin: every block gets a sample of the whole plane.
+    int64_t ch = (a.n + cap * 32 - 1) / (cap * 32);
+    ch = (ch + per_round - 1) / per_round * per_round;
+    p.chunk = ch;
+    p.nchunks = (a.n + ch - 1) / ch;
+    grid = (int)(p.nchunks < cap ? p.nchunks : cap);
+  }
   p.scale_a = a.scale_a;
   p.scale_b = a.scale_b;
   p.inertia_scale = a.h_inertia_scale;

@@ -35,6 +35,9 @@ struct km_ctx {
   bool have_bbox = false;
   bool have_points = false;
   int32_t *labels = nullptr;  // device, n
+  unsigned *perm = nullptr;   // device, n: original row of each stored row once the store was cell-sorted (km_sort.cu)
+  KmPrune2 sort_pr;           // the grid the stored order follows
+  int passes_since_upload = 0;
   void *pinned = nullptr;     // staging for uploads / downloads
   size_t pinned_bytes = 0;
 
@@ -119,6 +122,7 @@ struct KmAssignArgs {
   float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
   KmPrune2 pr;
+  int sorted;          // ... and the points are stored in ascending cell order of `pr`
   cudaStream_t stream;
 };
 
@@ -139,3 +143,11 @@ cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int3
                                 double sigma, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t *launches);
+
+// km_sort.cu: one-time reordering of owned d = 2 points by candidate-grid cell
+cudaError_t km_sort_points_by_cell(float **x, int32_t **labels, int64_t n, const KmPrune2 &pr, unsigned **perm_out,
+                                   int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_unpermute_labels(const int32_t *labels_sorted, const unsigned *perm, int64_t n, int32_t *out_dev,
+                                int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_unpermute_rows2(const float *x_sorted, const unsigned *perm, int64_t n, int64_t i0, int64_t cnt,
+                               float *out_dev, int sm_count, cudaStream_t s, int64_t *launches);

@@ -345,7 +345,8 @@ def test_config2_full_size_bit_exact(km):
 def test_large_properties_d2_k64(km):
     """configs[4] per-GPU shape scaled to what one test may take: size-independent
     properties — inertia never rises, counts sum to N, convergence is a fixed point,
-    incremental == full — plus label parity on a sampled prefix."""
+    incremental == full — plus label parity of every point after 13 iterations
+    (the store is cell-sorted and dealt out in round-robin chunks by then)."""
     n = 8_000_000
     with km.KMeansState() as st, km.KMeansState(update_mode=1) as full:
         for s in (st, full):
@@ -362,9 +363,10 @@ def test_large_properties_d2_k64(km):
         # the labels of a prefix equal the oracle's argmin under the centroids that made them
         c_before = st.centroids()
         st.assign()
-        lab = st.labels()[:200000]
-        xs = st.get_points(0, 200000)
-        olab, _, _ = oracle.assign(xs, c_before)
+        lab = st.labels()
+        xs = st.get_points()
+        assert np.array_equal(xs[:100000], oracle.gen_blobs(5, 100000, 2, 64))   # rows come back in generation order
+        olab, _, _ = oracle.assign(xs, c_before, nthreads=0)
         assert np.array_equal(lab, olab)
 
 
@@ -419,6 +421,57 @@ def test_pruned_adversarial_geometry(km):
     o = oracle.run(xf, cf, max_iter=25)
     assert np.array_equal(g["labels"], o["labels"]) and g["iterations"] == o["iterations"]
     assert close(g["centroids"], o["centroids"])
+
+
+def test_sorted_store_is_invisible(km):
+    """The pruned path re-orders its copy of the points by grid cell before the third pass on an
+    upload (km_sort.cu).  Labels, rows and Forgy picks must keep coming back in the caller's order,
+    before and after, and a borrowed (attached) buffer is never re-ordered."""
+    n, k = 50000, 64
+    x = oracle.gen_blobs(41, n, 2, k)
+    c0 = oracle.forgy_init(x, k, 9)
+    with km.KMeansState(prune_min_points=1) as st:
+        st.upload_points(x)
+        st.set_centroids(c0)
+        c = c0.copy()
+        lab_prev = np.full(n, -1, np.int32)
+        for it in range(6):   # passes 1-2 run on the uploaded order, 3+ on the sorted store
+            s = st.assign()
+            olab, _, _ = oracle.assign(x, c)
+            assert np.array_equal(st.labels(), olab), "pass %d" % it
+            assert s["changed"] == int(np.sum(olab != lab_prev))
+            lab_prev = olab
+            st.update()
+            c, _ = oracle.update(x, olab, c, sum_mode=oracle.SUM_EXACT)
+            assert np.array_equal(st.centroids(), c)
+        assert np.array_equal(st.get_points(), x)
+        assert np.array_equal(st.get_points(1234, 777), x[1234:2011])
+        st.init_forgy(k, 9)   # picks rows by their ORIGINAL index
+        assert np.array_equal(st.centroids(), c0)
+        # a second upload of the same shape starts over in the caller's order
+        x2 = oracle.gen_blobs(42, n, 2, k)
+        st.upload_points(x2)
+        st.set_centroids(c0)
+        r = st.run(40)
+        o = oracle.run(x2, c0, max_iter=40)
+        assert r["iterations"] == o["iterations"] and np.array_equal(st.labels(), o["labels"])
+        assert np.array_equal(st.get_points(), x2)
+
+
+def test_pruned_attached_points_stay_unsorted(km):
+    import torch
+    n, k = 40000, 32
+    x = oracle.gen_blobs(77, n, 2, k)
+    c0 = oracle.forgy_init(x, k, 2)
+    xt = torch.from_numpy(x).cuda()
+    with km.KMeansState(prune_min_points=1) as st:
+        st.attach_points(xt.data_ptr(), n, 2)
+        st.set_centroids(c0)
+        r = st.run(40)
+        o = oracle.run(x, c0, max_iter=40)
+        assert r["iterations"] == o["iterations"] and np.array_equal(st.labels(), o["labels"])
+        assert close(st.centroids(), o["centroids"])
+    assert np.array_equal(xt.cpu().numpy(), x)
 
 
 # ---------------------------------------------------------------- tensor path (tcgen05 coarse stage + exact stage)
