@@ -56,6 +56,14 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
   return r;
 }
 
+// fire-and-forget 8-byte global -> shared copy (LDGSTS): no register holds the value in flight
+__device__ __forceinline__ void km_cp_async8(void *smem_dst, const void *gsrc) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void km_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void km_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 template <int D>
 struct KmSmallCfg {
   static constexpr int PPV = (D == 1) ? 4 : (D == 2) ? 2 : 1;   // points per 16-byte vector (else 1 row per "vector")
@@ -103,7 +111,7 @@ struct KmBatch {
 // Load the thread's NV vectors of round `r0` (first point index of the round) within the
 // block's chunk [.., c1).  A vector wholly inside the chunk is one 16-byte load (d = 1, 2, 4)
 // or a few 8/16-byte loads (other even d); the ragged end is read point by point.
-template <int D>
+template <int D, bool LABELS = true>
 __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__restrict__ xb,
                                               const int32_t *__restrict__ lb, int r, int cn) {
   using Cfg = KmSmallCfg<D>;
@@ -117,13 +125,17 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
       if constexpr (D == 1) {
         const float4 q = __ldg(reinterpret_cast<const float4 *>(row));
         b.xs[v * 4 + 0] = q.x; b.xs[v * 4 + 1] = q.y; b.xs[v * 4 + 2] = q.z; b.xs[v * 4 + 3] = q.w;
-        const int4 o = *reinterpret_cast<const int4 *>(lb + i0);
-        b.old[v * 4 + 0] = o.x; b.old[v * 4 + 1] = o.y; b.old[v * 4 + 2] = o.z; b.old[v * 4 + 3] = o.w;
+        if (LABELS) {
+          const int4 o = *reinterpret_cast<const int4 *>(lb + i0);
+          b.old[v * 4 + 0] = o.x; b.old[v * 4 + 1] = o.y; b.old[v * 4 + 2] = o.z; b.old[v * 4 + 3] = o.w;
+        }
       } else if constexpr (D == 2) {
         const ulonglong2 q = __ldg(reinterpret_cast<const ulonglong2 *>(row));
         b.xq[v * 2 + 0][0] = q.x; b.xq[v * 2 + 1][0] = q.y;
-        const int2 o = *reinterpret_cast<const int2 *>(lb + i0);
-        b.old[v * 2 + 0] = o.x; b.old[v * 2 + 1] = o.y;
+        if (LABELS) {
+          const int2 o = *reinterpret_cast<const int2 *>(lb + i0);
+          b.old[v * 2 + 0] = o.x; b.old[v * 2 + 1] = o.y;
+        }
       } else {
         if constexpr (D % 4 == 0) {
 #pragma unroll
@@ -139,7 +151,7 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
           for (int m = 0; m < NP; m++) b.xq[v][m] = pk2(__ldg(row + 2 * m), __ldg(row + 2 * m + 1));
           b.xs[v] = __ldg(row + D - 1);
         }
-        b.old[v] = lb[i0];
+        if (LABELS) b.old[v] = lb[i0];
       }
     } else {
 #pragma unroll
@@ -147,12 +159,40 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
         const int i = i0 + u;
         const bool live = i < cn;
         const int q = v * PPV + u;
-        b.old[q] = live ? lb[i] : 0;
+        if (LABELS) b.old[q] = live ? lb[i] : 0;
 #pragma unroll
         for (int m = 0; m < NP; m++)
           b.xq[q][m] = live ? pk2(xb[i * D + 2 * m], xb[i * D + 2 * m + 1]) : pk2(0.f, 0.f);
         if (D == 1 || TAIL) b.xs[q] = live ? xb[i * D + D - 1] : 0.f;
       }
+    }
+  }
+}
+
+// The previous labels of the thread's points alone (same indexing as km_load_batch).  The pruned
+// kernel fetches them at the top of the round they are used in rather than a round ahead: they
+// are not needed before the tail, and four fewer live registers keep the prefetched labels from
+// being spilled (a spill store waits for the load it spills — the prefetch would be lost).
+template <int D>
+__device__ __forceinline__ void km_load_labels(KmBatch<D> &b, const int32_t *__restrict__ lb, int r, int cn) {
+  using Cfg = KmSmallCfg<D>;
+  constexpr int PPV = Cfg::PPV, NV = Cfg::NV;
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    const int i0 = r + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;
+    if (i0 + PPV <= cn) {
+      if constexpr (PPV == 4) {
+        const int4 o = *reinterpret_cast<const int4 *>(lb + i0);
+        b.old[v * 4 + 0] = o.x; b.old[v * 4 + 1] = o.y; b.old[v * 4 + 2] = o.z; b.old[v * 4 + 3] = o.w;
+      } else if constexpr (PPV == 2) {
+        const int2 o = *reinterpret_cast<const int2 *>(lb + i0);
+        b.old[v * 2 + 0] = o.x; b.old[v * 2 + 1] = o.y;
+      } else {
+        b.old[v] = lb[i0];
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < PPV; u++) b.old[v * PPV + u] = (i0 + u < cn) ? lb[i0 + u] : 0;
     }
   }
 }
@@ -185,22 +225,26 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   // inside the chunk is addressed with 32-bit offsets from the chunk's base
   constexpr int per_round = KM_SMALL_THREADS * PPT;
   auto chunk_len = [&](int64_t c) { return (int)max((int64_t)0, min(p.n - c * p.chunk, p.chunk)); };
-  // the two ends of a chunk of cell-sorted points give the cells it touches
-  auto chunk_ends = [&](int64_t c, float2 &first, float2 &last) {
+  // The two ends of a chunk of cell-sorted points give the cells it touches.  Thread 0 fetches
+  // them a chunk ahead straight into shared memory (asynchronous copy: nothing to keep in
+  // registers, nothing to wait for until the chunk starts).
+  __shared__ float2 s_ends[2];
+  auto fetch_chunk_ends = [&](int64_t c) {
     const int len = chunk_len(c);
-    if (len > 0) {
+    if (threadIdx.x == 0 && len > 0) {
       const float2 *xc = reinterpret_cast<const float2 *>(p.x) + c * p.chunk;
-      first = __ldg(xc);
-      last = __ldg(xc + (len - 1));
+      km_cp_async8(&s_ends[0], xc);
+      km_cp_async8(&s_ends[1], xc + (len - 1));
+      km_cp_async_commit();
     }
   };
 
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
-  float2 end_a = make_float2(0.f, 0.f), end_z = make_float2(0.f, 0.f);
-  km_load_batch<D>(cur, p.x + (int64_t)blockIdx.x * p.chunk * D, p.labels + (int64_t)blockIdx.x * p.chunk, 0,
-                   chunk_len(blockIdx.x));
-  if (PRUNE && p.sorted) chunk_ends(blockIdx.x, end_a, end_z);
+  constexpr bool EARLY_LABELS = !PRUNE;   // see km_load_labels
+  km_load_batch<D, EARLY_LABELS>(cur, p.x + (int64_t)blockIdx.x * p.chunk * D, p.labels + (int64_t)blockIdx.x * p.chunk, 0,
+                                 chunk_len(blockIdx.x));
+  if (PRUNE && p.sorted) fetch_chunk_ends(blockIdx.x);
 
   // ---- prologue = the previous pass's centroid update (a4), redone by every block:
   //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
@@ -372,9 +416,10 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   if constexpr (PRUNE) {
     if (p.sorted) {
       // candidate words for the cells between this chunk's first and last point
-      if (ch != (int64_t)blockIdx.x) __syncthreads();   // the previous chunk's readers are done
-      cell_lo_b = cell_of(end_a);
-      cell_hi_b = max(cell_of(end_z), cell_lo_b);
+      if (threadIdx.x == 0) km_cp_async_wait_all();
+      __syncthreads();   // the chunk's ends have landed; the previous chunk's readers are done
+      cell_lo_b = cell_of(s_ends[0]);
+      cell_hi_b = max(cell_of(s_ends[1]), cell_lo_b);
       build_cells_range(cell_lo_b, cell_hi_b);
       __syncthreads();
     }
@@ -383,11 +428,12 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     // software pipeline: the next round's loads (the next chunk's first, at the end of this
     // one) are in flight during this round's arithmetic
     KmBatch<D> nxt;
+    if (!EARLY_LABELS) km_load_labels<D>(cur, lb, r0, cn);
     if (r0 + per_round < cn) {
-      km_load_batch<D>(nxt, xb, lb, r0 + per_round, cn);
+      km_load_batch<D, EARLY_LABELS>(nxt, xb, lb, r0 + per_round, cn);
     } else if (ch_next < p.nchunks) {
-      km_load_batch<D>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
-      if (PRUNE && p.sorted) chunk_ends(ch_next, end_a, end_z);
+      km_load_batch<D, EARLY_LABELS>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
+      if (PRUNE && p.sorted) fetch_chunk_ends(ch_next);
     }
 
     // ---- binary32 filter, top-2 on integer keys
@@ -400,9 +446,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       // each point looks only at its cell's candidates; a cell that overflowed its word
       // (count byte 0xFF) sends its points to the binary64 scan of all k below
       const KmPrune2 &pr = p.pr;
-      unsigned long long w[PPT];
-#pragma unroll
-      for (int q = 0; q < PPT; q++) {
+      auto cell_of_q = [&](int q) {
         float x0, x1;
         unpk2(cur.xq[q][0], x0, x1);
         // every real point maps inside the grid; the clamp is for the zero-filled lanes past
@@ -411,17 +455,36 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         const int iy = min(__float_as_int(fmaf(x1, pr.sy, pr.kym)) & 0x3FFFFF, pr.gp - 1);
         int cell = iy * pr.gp + ix;
         if (p.sorted) cell = min(max(cell, cell_lo_b), cell_hi_b);   // dead lanes only: stay inside what was built
-        w[q] = cells[cell];
-      }
+        return cell;
+      };
       // Do all 32 x PPT points of the warp share one candidate word?  With the points stored in
       // cell order nearly every warp does: the candidates are then warp-uniform (one broadcast
       // LDS each, no predication), and a single-candidate word needs no filter at all.
-      const unsigned long long w0 = __shfl_sync(0xffffffffu, w[0], 0);
-      bool same = true;
+      unsigned long long w[PPT], w0 = 0;
+      bool uniform = false;
+      if (p.sorted && r0 + per_round <= cn) {
+        // cell ids ascend along the store and every slot of a whole round is a real point: if
+        // the warp's first and last point share a cell, so does everything between them
+        const int ca = __shfl_sync(0xffffffffu, cell_of_q(0), 0);
+        const int cz = __shfl_sync(0xffffffffu, cell_of_q(PPT - 1), 31);
+        if (ca == cz) {
+          uniform = true;
+          w0 = cells[ca];
 #pragma unroll
-      for (int q = 0; q < PPT; q++) same &= (w[q] == w0);
+          for (int q = 0; q < PPT; q++) w[q] = w0;
+        }
+      }
+      if (!uniform) {
+#pragma unroll
+        for (int q = 0; q < PPT; q++) w[q] = cells[cell_of_q(q)];
+        w0 = __shfl_sync(0xffffffffu, w[0], 0);
+        bool same = true;
+#pragma unroll
+        for (int q = 0; q < PPT; q++) same &= (w[q] == w0);
+        uniform = __all_sync(0xffffffffu, same);
+      }
       const int n0 = (int)(w0 & 0xFF);
-      if (__all_sync(0xffffffffu, same) && n0 != 0xFF) {
+      if (uniform && n0 != 0xFF) {
         if (n0 == 1 && p.exact_inertia) {
           // the only candidate wins: key = its index under distance bits 0 ("clear" below)
 #pragma unroll
