@@ -18,6 +18,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib as L
+from . import board_json
 
 
 class KMeansError(RuntimeError):
@@ -260,3 +261,29 @@ def run(state, max_iter=300):
     return dict(labels=state.labels(), centroids=state.centroids(), iterations=s["iterations"],
                 inertia=s["inertia"], converged=bool(s["converged"]), changed=s["changed"],
                 rescored=s["rescored"], counts=state.counts(), device_ms=s["device_ms"])
+
+
+# ---- the reference's on-disk format ------------------------------------------
+def export_board(state, iteration=None, inertia=None):
+    """The state as the `{cards, centroids, meta}` object the demo's Import button accepts
+    (/root/reference/app.mjs:263-283); see board_json.py for the mapping.  Meant for boards a
+    person can look at: one JSON object per point."""
+    return board_json.export_board(state.get_points(), state.labels(), state.centroids(),
+                                   iteration=0 if iteration is None else iteration, inertia=inertia,
+                                   counts=state.counts())
+
+
+def import_board(board, **ctx_kwargs):
+    """A board exported by export_board -> (state, info): points uploaded, centroids installed.
+    Labels are recomputed by the next assign() (a context's labels are its own)."""
+    info = board_json.import_board(board)
+    if info["points"] is None or info["centroids"] is None:
+        raise ValueError("import_board: the board carries no numeric points / centroid coordinates")
+    st = KMeansState(**ctx_kwargs)
+    try:
+        st.upload_points(info["points"])
+        st.set_centroids(info["centroids"])
+    except Exception:
+        st.close()
+        raise
+    return st, info

@@ -297,6 +297,22 @@ def test_facade_entry_points(km):
 
 
 # ---------------------------------------------------------------- error behaviour
+def test_board_export_import_round_trip(km):
+    """f3: a finished run written in the demo's {cards, centroids, meta} schema and read back."""
+    x = oracle.gen_blobs(6, 300, 2, 3)
+    st = km.init(x, 3, seed=1)
+    out = km.run(st, max_iter=50)
+    board = km.board_json.loads(km.board_json.dumps(km.export_board(st, iteration=out["iterations"], inertia=out["inertia"])))
+    assert [c["count"] for c in board["centroids"]] == out["counts"].tolist()
+    assert board["meta"]["iteration"] == out["iterations"]
+    st.close()
+    st2, info = km.import_board(board)
+    assert np.array_equal(info["points"], x) and np.array_equal(info["labels"], out["labels"])
+    s = st2.assign()   # the imported centroids are the converged ones: nothing is left to move
+    assert np.array_equal(st2.labels(), out["labels"]) and s["inertia"] == out["inertia"]
+    st2.close()
+
+
 def test_errors(km):
     L = km._lib
     with km.KMeansState() as st:
