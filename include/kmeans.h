@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define KM_ABI_VERSION 2
+#define KM_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define KM_API __attribute__((visibility("default")))
@@ -129,6 +129,12 @@ KM_API km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t n);
 KM_API km_status km_set_centroids(km_ctx *ctx, const double *c, int32_t k);
 /* seeded Forgy: first k picks of a partial Fisher-Yates over the job's point indices */
 KM_API km_status km_init_forgy(km_ctx *ctx, int32_t k, uint64_t seed);
+/* seeded k-means++: first centre = point floor(u*N), every further one drawn
+ * with probability proportional to its squared distance to the nearest centre so far.  The
+ * distances are quantised to integers before they are summed, so the draw does not depend on
+ * how the points are split over blocks or GPUs (oracle: ko_kmeanspp_indices).  No counterpart in
+ * the reference beyond its seeded-draw idiom (app.mjs:163). */
+KM_API km_status km_init_kmeanspp(km_ctx *ctx, int32_t k, uint64_t seed);
 
 /* ---- a3: assignment step (analog: updateCardAssign app.mjs:146-156, drop :358-372) -- */
 /* label[i] = argmin_j sum_t (x_it - c_jt)^2, strict <, lowest j wins ties; also counts
@@ -163,6 +169,10 @@ KM_API km_status km_get_counts(km_ctx *ctx, int64_t *out);
  * ratio = min ? max/min : (max ? Infinity : 1) */
 KM_API km_status km_get_balance(km_ctx *ctx, int64_t *max_out, int64_t *min_out, int64_t *gap_out,
                          double *ratio_out);
+/* per-cluster inertia: out[j] = sum over the members of cluster j of their squared distance to
+ * centroid j, for the current labels and centroids — the numeric stand-in for the dashboard's
+ * per-cluster cohesion (app.mjs:462-475, 485-487); sums to km_stats.inertia of the last assign */
+KM_API km_status km_get_cluster_inertia(km_ctx *ctx, double *out /* k */);
 /* raw order-free sums of the whole job: k*d `a` limbs, k*d `b` limbs, then the fixed-point
  * parameters {E, NB, QB, qa} (for bit-level parity tests) */
 KM_API km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t params4[4]);

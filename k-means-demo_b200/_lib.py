@@ -14,7 +14,7 @@ ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_OOM, ERR_STATE, ERR_NONFINITE, ERR_UNSU
 DTYPE_F32, DTYPE_F64 = 0, 1
 PATH_AUTO, PATH_DIRECT_F64, PATH_FILTER_F32, PATH_TENSOR = 0, 1, 2, 3
 UPDATE_INCREMENTAL, UPDATE_FULL = 0, 1
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class Config(C.Structure):
@@ -54,6 +54,7 @@ PROTOTYPES = {
     "km_get_points": (_i32, [_vp, _vp, _i64, _i64]),
     "km_set_centroids": (_i32, [_vp, _vp, _i32]),
     "km_init_forgy": (_i32, [_vp, _i32, _u64]),
+    "km_init_kmeanspp": (_i32, [_vp, _i32, _u64]),
     "km_assign": (_i32, [_vp, C.POINTER(Stats)]),
     "km_update": (_i32, [_vp, C.POINTER(Stats)]),
     "km_step": (_i32, [_vp, C.POINTER(Stats)]),
@@ -65,6 +66,7 @@ PROTOTYPES = {
     "km_get_centroids": (_i32, [_vp, _vp]),
     "km_get_counts": (_i32, [_vp, _vp]),
     "km_get_balance": (_i32, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_dbl)]),
+    "km_get_cluster_inertia": (_i32, [_vp, _vp]),
     "km_get_sums": (_i32, [_vp, _vp, _vp, _vp]),
     "km_lloyd_step_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "km_sync": (_i32, [_vp]),

@@ -136,6 +136,10 @@ class KMeansState:
         self._check(self._lib.km_init_forgy(self._h, k, seed))
         self.k = k
 
+    def init_kmeanspp(self, k, seed):
+        self._check(self._lib.km_init_kmeanspp(self._h, k, seed))
+        self.k = k
+
     # -- a3 / a4 / a5
     def _stats_call(self, fn, *args):
         s = L.Stats()
@@ -184,6 +188,28 @@ class KMeansState:
         self._check(self._lib.km_get_balance(self._h, C.byref(mx), C.byref(mn), C.byref(gap), C.byref(ratio)))
         return dict(max=mx.value, min=mn.value, gap=gap.value, ratio=ratio.value)
 
+    def cluster_inertia(self):
+        out = np.empty(self.k, dtype=np.float64)
+        self._check(self._lib.km_get_cluster_inertia(self._h, _ptr(out)))
+        return out
+
+    def snapshot(self):
+        """The numeric form of the dashboard's snapshotMetrics() (/root/reference/app.mjs:481-496):
+        `counts`, `balance{max,min,gap,ratio}` with the same formulas, and — where the demo has a
+        per-cluster cohesion and its average — `inertia` per cluster and its mean over clusters."""
+        inertia = self.cluster_inertia()
+        return dict(counts=self.counts(), inertia=inertia, balance=self.balance(),
+                    avg_inertia=float(inertia.mean()) if inertia.size else 0.0, total_inertia=float(inertia.sum()))
+
+    @staticmethod
+    def deltas(prev, now):
+        """What the dashboard prints next to its chips when a previous snapshot exists
+        (app.mjs:516-521): change of the balance gap (<= 0 is "tighter") and of the average
+        tightness; here also per-cluster count and inertia changes."""
+        return dict(gap=int(now["balance"]["gap"] - prev["balance"]["gap"]),
+                    avg_inertia=float(now["avg_inertia"] - prev["avg_inertia"]),
+                    counts=now["counts"] - prev["counts"], inertia=now["inertia"] - prev["inertia"])
+
     def sums(self):
         sa = np.empty((self.k, self.d), dtype=np.int64)
         sb = np.empty((self.k, self.d), dtype=np.int64)
@@ -223,8 +249,10 @@ def host_free(addr):
 
 
 # ---- the facade proper: same four entry points as kmeans.mjs ---------------------------
-def init(points, k, seed=None, centroids=None, **ctx_kwargs):
-    """init(points, k, {seed} | {centroids}) -> state."""
+def init(points, k, seed=None, centroids=None, method="forgy", **ctx_kwargs):
+    """init(points, k, {seed} | {centroids}) -> state.  `method`: "forgy" or "kmeans++" (seeded)."""
+    if method not in ("forgy", "kmeans++"):
+        raise ValueError("init: method must be 'forgy' or 'kmeans++'")
     if (seed is None) == (centroids is None):
         raise ValueError("init: pass exactly one of seed= or centroids=")
     st = KMeansState(**ctx_kwargs)
@@ -235,6 +263,8 @@ def init(points, k, seed=None, centroids=None, **ctx_kwargs):
             if c.shape[0] != k:
                 raise ValueError("init: centroids must have k rows")
             st.set_centroids(c)
+        elif method == "kmeans++":
+            st.init_kmeanspp(k, seed)
         else:
             st.init_forgy(k, seed)
     except Exception:

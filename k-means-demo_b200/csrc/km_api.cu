@@ -669,6 +669,127 @@ extern "C" km_status km_init_forgy(km_ctx *ctx, int32_t k, uint64_t seed) {
   return install_centroids(ctx, c.data(), k);
 }
 
+// put a cell-sorted store back into the caller's row order (k-means++ walks rows in that order)
+static km_status restore_caller_order(km_ctx *ctx) {
+  if (!ctx->perm) return KM_OK;
+  float *x2 = nullptr;
+  int32_t *l2 = nullptr;
+  KM_CUDA(ctx, cudaMalloc(&x2, std::max<size_t>((size_t)ctx->n * 2 * sizeof(float), 16)));
+  cudaError_t e = cudaMalloc(&l2, std::max<size_t>((size_t)ctx->n * sizeof(int32_t), 16));
+  if (e == cudaSuccess) e = km_unpermute_rows2((const float *)ctx->x, ctx->perm, ctx->n, 0, ctx->n, x2, ctx->sm_count, ctx->stream, &ctx->launches);
+  if (e == cudaSuccess) e = km_unpermute_labels(ctx->labels, ctx->perm, ctx->n, l2, ctx->sm_count, ctx->stream, &ctx->launches);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) { cudaFree(x2); if (l2) cudaFree(l2); KM_CUDA(ctx, e); }
+  cudaFree(ctx->x);
+  cudaFree(ctx->labels);
+  cudaFree(ctx->perm);
+  ctx->x = x2; ctx->labels = l2; ctx->perm = nullptr;
+  ctx->passes_since_upload = 0;
+  return KM_OK;
+}
+
+// A7b (oracle: ko_kmeanspp_indices).  Init is not the timed path: one pass over the shard per
+// centre, a few small copies and (world > 1) two tiny all-reduces per centre.
+extern "C" km_status km_init_kmeanspp(km_ctx *ctx, int32_t k, uint64_t seed) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "km_init_kmeanspp: no points");
+  if (k < 1 || k > KM_MAX_K || k > ctx->n_total) return fail(ctx, KM_ERR_INVALID_ARG, "km_init_kmeanspp: need 1 <= k <= N");
+  km_status st = restore_caller_order(ctx);
+  if (st != KM_OK) return st;
+  const int32_t d = ctx->d;
+  const int64_t n = ctx->n;
+  const size_t row = (size_t)d * elt_size(ctx->dtype);
+  const int64_t tiles = (n + KM_PP_TILE - 1) / KM_PP_TILE;
+  int dbits = 0;
+  while ((1 << dbits) <= d) dbits++;
+  const double scale = ldexp(1.0, 62 - ctx->NB - (2 * ctx->E + 2 + dbits));
+  double *D = nullptr, *c_dev = nullptr;
+  long long *partial = nullptr, *small = nullptr;   // small: [0] = found index, [1 .. world] = per-rank totals
+  std::vector<long long> h_partial((size_t)std::max<int64_t>(tiles, 1)), h_small((size_t)ctx->world + 1);
+  std::vector<double> c((size_t)k * d, 0.0), crow((size_t)d);
+  std::vector<char> tmp(row);
+  auto cleanup = [&]() { if (D) cudaFree(D); if (c_dev) cudaFree(c_dev); if (partial) cudaFree(partial); if (small) cudaFree(small); };
+#define KM_PP_CUDA(expr)                                                          \
+  do {                                                                            \
+    cudaError_t _e = (expr);                                                      \
+    if (_e != cudaSuccess) { cleanup(); KM_CUDA(ctx, _e); }                       \
+  } while (0)
+  KM_PP_CUDA(cudaMalloc(&D, std::max<size_t>((size_t)n * sizeof(double), 16)));
+  KM_PP_CUDA(cudaMalloc(&c_dev, (size_t)d * sizeof(double)));
+  KM_PP_CUDA(cudaMalloc(&partial, (size_t)std::max<int64_t>(tiles, 1) * sizeof(long long)));
+  KM_PP_CUDA(cudaMalloc(&small, ((size_t)ctx->world + 1) * sizeof(long long)));
+  uint64_t state = seed;
+  for (int32_t s = 0; s < k; s++) {
+    const uint64_t r = km_splitmix64(state);
+    state += KM_GAMMA;
+    const double u = (double)(r >> 11) * 0x1.0p-53;
+    int64_t pick_local = -1;   // row of this shard that becomes centre s, or -1 if another rank owns it
+    bool by_global_index = (s == 0);
+    if (s > 0) {
+      KM_PP_CUDA(cudaMemcpyAsync(c_dev, c.data() + (size_t)(s - 1) * d, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+      KM_PP_CUDA(km_launch_pp_update(ctx->x, ctx->dtype, n, d, c_dev, D, scale, s == 1, partial, ctx->stream, &ctx->launches));
+      if (tiles > 0)
+        KM_PP_CUDA(cudaMemcpyAsync(h_partial.data(), partial, (size_t)tiles * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+      KM_PP_CUDA(cudaStreamSynchronize(ctx->stream));
+      long long mine = 0;
+      for (int64_t b = 0; b < tiles; b++) mine += h_partial[(size_t)b];
+      std::vector<long long> totals((size_t)ctx->world, 0);
+      totals[(size_t)ctx->rank] = mine;
+      if (ctx->world > 1) {   // every rank fills its own slot: the sum is the list of totals
+        KM_PP_CUDA(cudaMemcpyAsync(small + 1, totals.data(), (size_t)ctx->world * sizeof(long long), cudaMemcpyHostToDevice, ctx->stream));
+        int rc = g_nccl.all_reduce(small + 1, small + 1, (size_t)ctx->world, KM_NCCL_INT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream);
+        if (rc != 0) { cleanup(); return fail(ctx, KM_ERR_NCCL, std::string("ncclAllReduce: ") + g_nccl.get_error_string(rc)); }
+        KM_PP_CUDA(cudaMemcpyAsync(totals.data(), small + 1, (size_t)ctx->world * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+        KM_PP_CUDA(cudaStreamSynchronize(ctx->stream));
+      }
+      unsigned __int128 T = 0;
+      for (int q = 0; q < ctx->world; q++) T += (unsigned __int128)(unsigned long long)totals[(size_t)q];
+      if (T == 0) {
+        by_global_index = true;   // every point already sits on a centre
+      } else {
+        long long target = (long long)(((unsigned __int128)(r >> 11) * T) >> 53);
+        int owner = ctx->world - 1;
+        for (int q = 0; q < ctx->world; q++) {
+          if (target < totals[(size_t)q]) { owner = q; break; }
+          target -= totals[(size_t)q];
+        }
+        if (owner == ctx->rank) {
+          int64_t b = 0;
+          while (b + 1 < tiles && target >= h_partial[(size_t)b]) { target -= h_partial[(size_t)b]; b++; }
+          const int64_t start = b * KM_PP_TILE;
+          const int count = (int)std::min<int64_t>(KM_PP_TILE, n - start);
+          KM_PP_CUDA(km_launch_pp_find(D, start, count, scale, target, small, ctx->stream, &ctx->launches));
+          KM_PP_CUDA(cudaMemcpyAsync(h_small.data(), small, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+          KM_PP_CUDA(cudaStreamSynchronize(ctx->stream));
+          pick_local = h_small[0];
+        }
+      }
+    }
+    if (by_global_index) {
+      const int64_t g = (int64_t)floor(u * (double)ctx->n_total);
+      if (g >= ctx->i0 && g < ctx->i0 + n) pick_local = g - ctx->i0;
+    }
+    for (int32_t t = 0; t < d; t++) crow[(size_t)t] = 0.0;
+    if (pick_local >= 0) {
+      KM_PP_CUDA(cudaMemcpyAsync(tmp.data(), (const char *)ctx->x + (size_t)pick_local * row, row, cudaMemcpyDeviceToHost, ctx->stream));
+      KM_PP_CUDA(cudaStreamSynchronize(ctx->stream));
+      for (int32_t t = 0; t < d; t++)
+        crow[(size_t)t] = ctx->dtype == KM_DTYPE_F32 ? (double)((const float *)tmp.data())[t] : ((const double *)tmp.data())[t];
+    }
+    if (ctx->world > 1) {   // exactly one rank owns the row; the others contribute exact zeros
+      KM_PP_CUDA(cudaMemcpyAsync(c_dev, crow.data(), (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+      int rc = g_nccl.all_reduce(c_dev, c_dev, (size_t)d, KM_NCCL_FLOAT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream);
+      if (rc != 0) { cleanup(); return fail(ctx, KM_ERR_NCCL, std::string("ncclAllReduce: ") + g_nccl.get_error_string(rc)); }
+      KM_PP_CUDA(cudaMemcpyAsync(crow.data(), c_dev, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+      KM_PP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    for (int32_t t = 0; t < d; t++) c[(size_t)s * d + t] = crow[(size_t)t];
+  }
+#undef KM_PP_CUDA
+  cleanup();
+  return install_centroids(ctx, c.data(), k);
+}
+
 // ------------------------------------------------------------------ a3/a4/a5: the iteration
 static km_status ready(km_ctx *ctx) {
   if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points: call km_upload_points / km_attach_points / km_generate_blobs");
@@ -1033,6 +1154,58 @@ extern "C" km_status km_get_counts(km_ctx *ctx, int64_t *out) {
   if (s != KM_OK) return s;
   const KmAccLayout L = km_acc_layout(ctx->k, ctx->d);
   for (int32_t j = 0; j < ctx->k; j++) out[j] = h[(size_t)L.cnt + j];
+  return KM_OK;
+}
+
+// (Sa * 2^QB + Sb) * 2^-shift rounded once to binary64, ties to even (host twin of km_fixed_to_double)
+static double host_fixed_to_double(long long Sa, long long Sb, int QB, int shift) {
+  const __int128 T = (__int128)Sa * ((__int128)1 << QB) + (__int128)Sb;
+  if (T == 0) return 0.0;
+  const bool neg = T < 0;
+  const unsigned __int128 m = neg ? (unsigned __int128)(-T) : (unsigned __int128)T;
+  int hb = 127;
+  while (!((m >> hb) & 1)) hb--;
+  double v;
+  if (hb <= 52) {
+    v = ldexp((double)(unsigned long long)m, -shift);
+  } else {
+    const int sh = hb - 52;
+    unsigned __int128 q = m >> sh;
+    const unsigned __int128 rem = m & ((((unsigned __int128)1) << sh) - 1), half = ((unsigned __int128)1) << (sh - 1);
+    if (rem > half || (rem == half && (q & 1))) q++;
+    v = ldexp((double)(unsigned long long)q, sh - shift);
+  }
+  return neg ? -v : v;
+}
+
+// f2: the numeric stand-in for the dashboard's per-cluster cohesion (/root/reference/app.mjs:462-475,
+// 485-487): how tight each cluster is — the inertia of its members about its centroid.
+extern "C" km_status km_get_cluster_inertia(km_ctx *ctx, double *out) {
+  KM_BIND(ctx);
+  km_status s = ready(ctx);
+  if (s != KM_OK) return s;
+  if (!out) return fail(ctx, KM_ERR_INVALID_ARG, "out is NULL");
+  if (ctx->labels_fresh) return fail(ctx, KM_ERR_STATE, "km_get_cluster_inertia: nothing assigned yet");
+  if ((s = p1_flush(ctx, -1, -1)) != KM_OK) return s;
+  KmAssignArgs a;
+  fill_assign_args(ctx, a);   // for the inertia scale (host bound on max|c|)
+  const int32_t k = ctx->k;
+  long long *table = nullptr;
+  KM_CUDA(ctx, cudaMalloc(&table, (size_t)2 * k * sizeof(long long)));
+  std::vector<long long> h((size_t)2 * k);
+  cudaError_t e = km_launch_cluster_inertia(ctx->x, ctx->dtype, ctx->labels, ctx->n, ctx->d, k,
+                                            ctx->p1 ? ctx->p1C[ctx->p1_s] : ctx->c64, a.h_inertia_scale, a.scale_b, table,
+                                            ctx->sm_count, ctx->stream, &ctx->launches);
+  int rc = 0;
+  if (e == cudaSuccess && ctx->world > 1)
+    rc = g_nccl.all_reduce(table, table, (size_t)2 * k, KM_NCCL_INT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream);
+  if (e == cudaSuccess && rc == 0) e = cudaMemcpyAsync(h.data(), table, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(table);
+  if (rc != 0) return fail(ctx, KM_ERR_NCCL, std::string("ncclAllReduce: ") + g_nccl.get_error_string(rc));
+  KM_CUDA(ctx, e);
+  for (int32_t j = 0; j < k; j++)
+    out[j] = host_fixed_to_double(h[(size_t)j], h[(size_t)k + j], ctx->QB, a.h_qi + ctx->QB);
   return KM_OK;
 }
 

@@ -144,6 +144,17 @@ cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int3
 cudaError_t km_launch_fill_i32(int32_t *p, int64_t n, int32_t v, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t *launches);
 
+// k-means++ passes (km_kernels_misc.cu)
+#define KM_PP_TILE 4096
+cudaError_t km_launch_pp_update(const void *x, int dtype, int64_t n, int32_t d, const double *c_dev, double *D,
+                                double scale, int first, long long *partial, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_pp_find(const double *D, int64_t start, int count, double scale, long long target,
+                              long long *out_idx, cudaStream_t s, int64_t *launches);
+
+cudaError_t km_launch_cluster_inertia(const void *x, int dtype, const int32_t *labels, int64_t n, int32_t d, int32_t k,
+                                      const double *c_dev, double scale_i, double scale_b, long long *table,
+                                      int sm_count, cudaStream_t s, int64_t *launches);
+
 // km_sort.cu: one-time reordering of owned d = 2 points by candidate-grid cell
 cudaError_t km_sort_points_by_cell(float **x, int32_t **labels, int64_t n, const KmPrune2 &pr, unsigned **perm_out,
                                    int sm_count, cudaStream_t s, int64_t *launches);

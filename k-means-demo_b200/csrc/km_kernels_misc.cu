@@ -146,3 +146,116 @@ cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t 
   (*launches)++;
   return cudaGetLastError();
 }
+
+// ------------------------------------------------------------------ a2 / f1: k-means++ passes
+// One pass per new centre: D_i = min(D_i, dist2(x_i, c)) in the oracle's binary64 operation
+// order, q_i = trunc(D_i * 2^qd) and the exact integer sum of q over each tile of KM_PP_TILE
+// consecutive points.  Integer sums are what make the draw independent of blocking and of the
+// number of GPUs (oracle: ko_kmeanspp_indices).
+template <typename T>
+__global__ void __launch_bounds__(256) km_pp_update_kernel(const T *__restrict__ x, int64_t n, int d,
+                                                           const double *__restrict__ c, double *__restrict__ D,
+                                                           double scale, int first, long long *__restrict__ partial) {
+  extern __shared__ double pp_smem[];
+  const double *pp_c = c;   // very wide rows: read the centre through the cache instead
+  if (d <= 4096) {
+    for (int t = threadIdx.x; t < d; t += blockDim.x) pp_smem[t] = c[t];
+    __syncthreads();
+    pp_c = pp_smem;
+  }
+  const int64_t start = (int64_t)blockIdx.x * KM_PP_TILE;
+  const int64_t end = min(n, start + KM_PP_TILE);
+  long long sum = 0;
+  for (int64_t i = start + threadIdx.x; i < end; i += blockDim.x) {
+    const double di = km_dist2_f64(x + i * d, pp_c, d);
+    double cur = first ? __longlong_as_double(0x7FF0000000000000LL) : D[i];
+    if (di < cur) { cur = di; D[i] = cur; }
+    sum += __double2ll_rz(cur * scale);
+  }
+  __shared__ long long red[8];
+  sum = km_warp_sum_ll(sum);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long tot = 0;
+    for (int w = 0; w < 8; w++) tot += red[w];
+    partial[blockIdx.x] = tot;
+  }
+}
+
+// least i in [start, start + count) whose running sum of q exceeds `target` (one thread: a tile)
+__global__ void km_pp_find_kernel(const double *__restrict__ D, int64_t start, int count, double scale,
+                                  long long target, long long *out_idx) {
+  long long run = 0, pick = start + count - 1;
+  for (int i = 0; i < count; i++) {
+    run += __double2ll_rz(D[start + i] * scale);
+    if (run > target) { pick = start + i; break; }
+  }
+  *out_idx = pick;
+}
+
+cudaError_t km_launch_pp_update(const void *x, int dtype, int64_t n, int32_t d, const double *c_dev, double *D,
+                                double scale, int first, long long *partial, cudaStream_t s, int64_t *launches) {
+  if (n == 0) return cudaSuccess;
+  const int64_t tiles = (n + KM_PP_TILE - 1) / KM_PP_TILE;
+  const size_t smem = d <= 4096 ? (size_t)d * sizeof(double) : 0;
+  if (dtype == KM_DTYPE_F32)
+    km_pp_update_kernel<float><<<(unsigned)tiles, 256, smem, s>>>((const float *)x, n, d, c_dev, D, scale, first, partial);
+  else
+    km_pp_update_kernel<double><<<(unsigned)tiles, 256, smem, s>>>((const double *)x, n, d, c_dev, D, scale, first, partial);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
+cudaError_t km_launch_pp_find(const double *D, int64_t start, int count, double scale, long long target,
+                              long long *out_idx, cudaStream_t s, int64_t *launches) {
+  km_pp_find_kernel<<<1, 1, 0, s>>>(D, start, count, scale, target, out_idx);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ a6 / f2: per-cluster inertia
+// sum over the members of cluster j of dist2(x_i, c_j), binary64 per point in the oracle's
+// operation order, summed as order-free fixed-point limbs (table: [k] coarse, [k] fine).
+template <typename T>
+__global__ void __launch_bounds__(256) km_cluster_inertia_kernel(const T *__restrict__ x, const int32_t *__restrict__ labels,
+                                                                 int64_t n, int d, int k, const double *__restrict__ c,
+                                                                 double scale_i, double scale_b, long long *__restrict__ table,
+                                                                 int use_smem) {
+  extern __shared__ long long ci_tab[];
+  if (use_smem) {
+    for (int e = threadIdx.x; e < 2 * k; e += blockDim.x) ci_tab[e] = 0;
+    __syncthreads();
+  }
+  long long *tab = use_smem ? ci_tab : table;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int lab = labels[i];
+    if (lab < 0) continue;
+    long long a, b;
+    km_fixed_split(km_dist2_f64(x + i * d, c + (size_t)lab * d, d), scale_i, scale_b, a, b);
+    km_atomic_add_ll(tab + lab, a);
+    km_atomic_add_ll(tab + k + lab, b);
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < 2 * k; e += blockDim.x)
+      if (ci_tab[e] != 0) km_atomic_add_ll(table + e, ci_tab[e]);
+  }
+}
+
+cudaError_t km_launch_cluster_inertia(const void *x, int dtype, const int32_t *labels, int64_t n, int32_t d, int32_t k,
+                                      const double *c_dev, double scale_i, double scale_b, long long *table /* 2k, zeroed here */,
+                                      int sm_count, cudaStream_t s, int64_t *launches) {
+  cudaError_t e = cudaMemsetAsync(table, 0, (size_t)2 * k * sizeof(long long), s);
+  if (e != cudaSuccess || n == 0) return e;
+  const int use_smem = (size_t)2 * k * sizeof(long long) <= 32 * 1024;
+  const size_t smem = use_smem ? (size_t)2 * k * sizeof(long long) : 0;
+  int64_t want = (n + 256 * 16 - 1) / (256 * 16);
+  int grid = (int)(want < 1 ? 1 : (want < (int64_t)sm_count * 8 ? want : (int64_t)sm_count * 8));
+  if (dtype == KM_DTYPE_F32)
+    km_cluster_inertia_kernel<float><<<grid, 256, smem, s>>>((const float *)x, labels, n, d, k, c_dev, scale_i, scale_b, table, use_smem);
+  else
+    km_cluster_inertia_kernel<double><<<grid, 256, smem, s>>>((const double *)x, labels, n, d, k, c_dev, scale_i, scale_b, table, use_smem);
+  (*launches)++;
+  return cudaGetLastError();
+}

@@ -36,6 +36,10 @@ def lib():
         L.ko_gen_blobs.argtypes = [u64, i64, i64, i32, i32, dbl, vp]
         L.ko_forgy_indices.restype = i32
         L.ko_forgy_indices.argtypes = [i64, i32, u64, vp]
+        L.ko_kmeanspp_indices.restype = i32
+        L.ko_kmeanspp_indices.argtypes = [vp, C.c_int, i64, i32, i32, u64, C.c_double, i64, vp]
+        L.ko_cluster_inertia.restype = None
+        L.ko_cluster_inertia.argtypes = [vp, C.c_int, i64, i32, vp, vp, i32, vp]
         L.ko_assign.restype = i64
         L.ko_assign.argtypes = [vp, C.c_int, i64, i32, vp, i32, vp, vp]
         L.ko_assign_mt.restype = i64
@@ -110,6 +114,33 @@ def forgy_indices(n, k, seed):
 def forgy_init(x, k, seed):
     idx = forgy_indices(x.shape[0], k, seed)
     return np.ascontiguousarray(x[idx].astype(np.float64))
+
+
+def kmeanspp_indices(x, k, seed, maxabs_=None, n_total=None):
+    """A7b: the k rows a seeded k-means++ (D^2 sampling on integer-quantised distances) picks."""
+    x, dt = _points(x)
+    n, d = x.shape
+    out = np.empty(k, dtype=np.int64)
+    m = maxabs(x) if maxabs_ is None else maxabs_
+    rc = lib().ko_kmeanspp_indices(_p(x), dt, n, d, k, seed, float(m), n if n_total is None else n_total, _p(out))
+    if rc != 0:
+        raise ValueError("kmeans++: need 1 <= k <= n")
+    return out
+
+
+def kmeanspp_init(x, k, seed):
+    idx = kmeanspp_indices(x, k, seed)
+    return np.ascontiguousarray(np.asarray(x)[idx].astype(np.float64))
+
+
+def cluster_inertia(x, labels, c):
+    """f2: per-cluster sum of the members' squared distances to their centroid (index order)."""
+    x, dt = _points(x)
+    c = np.ascontiguousarray(c, dtype=np.float64)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    out = np.empty(c.shape[0], dtype=np.float64)
+    lib().ko_cluster_inertia(_p(x), dt, x.shape[0], x.shape[1], _p(labels), _p(c), c.shape[0], _p(out))
+    return out
 
 
 def maxabs(x):

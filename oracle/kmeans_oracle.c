@@ -143,6 +143,66 @@ static inline double dist2(const void *x, int dtype, size_t row, int32_t d, cons
   return acc;
 }
 
+/* ------------------------------------------------------------------ A7b: k-means++ (f1)
+ * OUR SPEC (the reference seeds nothing numerically; its only seeded-choice idiom is the
+ * Math.random() draw of /root/reference/app.mjs:163, kept here as u = 53 bits / 2^53):
+ *   u_0, u_1, ... from splitmix64 exactly as in A7;  first centre = point floor(u_0 * N)
+ *   for s = 1 .. k-1:
+ *     D_i  = min(D_i, dist2(x_i, centre_{s-1}))            binary64, A1 operation order
+ *     q_i  = trunc(D_i * 2^qd)  (int64),  qd = 62 - NB - (2E + 2 + bitlen(d)):  q_i sums to < 2^62
+ *     T    = sum_i q_i                                      exact integers: order-free
+ *     if T == 0: next = floor(u_s * N)  (every point sits on a centre already)
+ *     else target = ((r_s >> 11) * T) >> 53  (128-bit product),  next = least i with q_0+..+q_i > target
+ * Quantising D to integers is what makes the draw independent of how the sum is split across
+ * blocks and GPUs (the same device the per-cluster sums use). */
+void ko_fixed_params(double maxabs, int64_t n_total, int32_t *E, int32_t *NB, int32_t *QB, int32_t *qa);
+
+int32_t ko_kmeanspp_indices(const void *x, int dtype, int64_t n, int32_t d, int32_t k, uint64_t seed,
+                            double maxabs, int64_t n_total, int64_t *out) {
+  if (k < 1 || k > n) return -1;
+  int32_t E, NB, QB, qa;
+  ko_fixed_params(maxabs, n_total, &E, &NB, &QB, &qa);
+  int32_t dbits = 0;
+  while (((int32_t)1 << dbits) <= d) dbits++;
+  const int32_t qd = 62 - NB - (2 * E + 2 + dbits);
+  double *D = (double *)malloc(sizeof(double) * (size_t)n);
+  double *c = (double *)malloc(sizeof(double) * (size_t)d);
+  if (!D || !c) { free(D); free(c); return -2; }
+  for (int64_t i = 0; i < n; i++) D[i] = INFINITY;
+  uint64_t state = seed;
+  for (int32_t s = 0; s < k; s++) {
+    uint64_t r = ko_splitmix64(state);
+    state += 0x9E3779B97F4A7C15ULL;
+    int64_t pick;
+    if (s == 0) {
+      pick = (int64_t)floor((double)(r >> 11) * 0x1.0p-53 * (double)n);
+    } else {
+      int64_t total = 0;
+      for (int64_t i = 0; i < n; i++) {
+        double di = dist2(x, dtype, (size_t)i, d, c);
+        if (di < D[i]) D[i] = di;
+        total += (int64_t)ldexp(D[i], qd); /* the cast truncates toward zero */
+      }
+      if (total == 0) {
+        pick = (int64_t)floor((double)(r >> 11) * 0x1.0p-53 * (double)n);
+      } else {
+        const int64_t target = (int64_t)(((unsigned __int128)(r >> 11) * (unsigned __int128)(uint64_t)total) >> 53);
+        int64_t run = 0;
+        pick = n - 1;
+        for (int64_t i = 0; i < n; i++) {
+          run += (int64_t)ldexp(D[i], qd);
+          if (run > target) { pick = i; break; }
+        }
+      }
+    }
+    out[s] = pick;
+    for (int32_t t = 0; t < d; t++) c[t] = load_x(x, dtype, (size_t)pick * (size_t)d + t);
+  }
+  free(D);
+  free(c);
+  return 0;
+}
+
 static inline int32_t argmin_row(const void *x, int dtype, size_t i, int32_t d, const double *c,
                                  int32_t k, double *best_out) {
   double best = INFINITY;
@@ -340,6 +400,18 @@ void ko_best_distances(const void *x, int dtype, int64_t n, int32_t d, const dou
     }
     best[i] = b1;
     if (second) second[i] = b2;
+  }
+}
+
+/* f2: per-cluster inertia for given labels and centroids — members' A1 distances to their own
+ * centroid, summed sequentially in index order (A6 restricted to one cluster) */
+void ko_cluster_inertia(const void *x, int dtype, int64_t n, int32_t d, const int32_t *labels,
+                        const double *c, int32_t k, double *out) {
+  for (int32_t j = 0; j < k; j++) out[j] = 0.0;
+  for (int64_t i = 0; i < n; i++) {
+    int32_t j = labels[i];
+    if (j < 0 || j >= k) continue;
+    out[j] = out[j] + dist2(x, dtype, (size_t)i, d, c + (size_t)j * d);
   }
 }
 

@@ -41,8 +41,9 @@ def main():
         r = nr.run(x, c0, max_iter=max_iter)
         lab1, changed1, inertia1 = nr.assign(x, c0)
         c1, counts1 = nr.update(x, lab1, c0)
+        kpp = nr.kmeanspp_indices(x, k, init_seed)   # A7b: seeded k-means++ picks for the same data
         np.savez_compressed(
-            os.path.join(HERE, name + ".npz"), x=x, c0=c0, forgy_idx=idx, labels=r["labels"],
+            os.path.join(HERE, name + ".npz"), x=x, c0=c0, forgy_idx=idx, kpp_idx=kpp, labels=r["labels"],
             centroids=r["centroids"], iterations=r["iterations"], inertia=r["inertia"], counts=r["counts"],
             changed=r["changed"], max_iter=max_iter, seed=seed, k_true=k_true, init_seed=init_seed,
             first_labels=lab1, first_inertia=inertia1, first_centroids=c1, first_counts=counts1)

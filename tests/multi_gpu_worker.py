@@ -37,6 +37,8 @@ def main():
             st.comm_init(bytes(uid.cpu().numpy().tobytes()), rank, world)
             x_local = oracle.gen_blobs(40 + ci, hi - lo, d, k, i0=lo)
             st.upload_points(x_local)
+            st.init_kmeanspp(k, 13)
+            cpp = st.centroids()
             st.init_forgy(k, 11)
             c0 = st.centroids()
             s = st.run(40)
@@ -49,6 +51,7 @@ def main():
         if rank == 0:
             x = oracle.gen_blobs(40 + ci, n, d, k)
             assert np.array_equal(c0, oracle.forgy_init(x, k, 11)), "forgy rows differ"
+            assert np.array_equal(cpp, oracle.kmeanspp_init(x, k, 13)), "k-means++ rows differ"
             ref = oracle.run(x, c0, max_iter=40)
             ex = oracle.run(x, c0, max_iter=40, sum_mode=oracle.SUM_EXACT, nthreads=0)
             got = torch.cat(gathered).cpu().numpy()

@@ -68,6 +68,13 @@ def test_golden(km, case, path):
     assert np.array_equal(r["counts"], g["counts"])
     assert close(r["centroids"], g["centroids"])
     assert r["inertia"] == pytest.approx(float(g["inertia"]), rel=REL)
+    if path == "auto":   # the seeded initialisations pick the golden rows
+        with km.KMeansState() as st:
+            st.upload_points(g["x"])
+            st.init_forgy(g["c0"].shape[0], int(g["init_seed"]))
+            assert np.array_equal(st.centroids(), g["x"][g["forgy_idx"]].astype(np.float64))
+            st.init_kmeanspp(g["c0"].shape[0], int(g["init_seed"]))
+            assert np.array_equal(st.centroids(), g["x"][g["kpp_idx"]].astype(np.float64))
 
 
 def test_a9_closed_form(km, golden_dir):
@@ -297,6 +304,82 @@ def test_facade_entry_points(km):
 
 
 # ---------------------------------------------------------------- error behaviour
+@pytest.mark.parametrize("shape", [(5000, 2, 8, np.float32), (3000, 5, 20, np.float32), (2000, 32, 16, np.float32),
+                                   (1500, 3, 7, np.float64), (64, 1, 64, np.float32), (20000, 2, 64, np.float32)],
+                         ids=lambda s: "n%d_d%d_k%d_%s" % (s[0], s[1], s[2], np.dtype(s[3]).name))
+def test_kmeanspp_picks_the_oracles_rows(km, shape):
+    """f1: seeded k-means++ (D^2 sampling on integer-quantised distances, A7b) — the very rows the
+    oracle picks, hence the very same run."""
+    n, d, k, dt = shape
+    x = oracle.gen_blobs(50 + d, n, d, max(2, k // 2)).astype(dt)
+    want = oracle.kmeanspp_init(x, k, 21)
+    with km.KMeansState() as st:
+        st.upload_points(x)
+        st.init_kmeanspp(k, 21)
+        assert np.array_equal(st.centroids(), want)
+        s = st.run(30)
+        o = oracle.run(x, want, max_iter=30)
+        assert s["iterations"] == o["iterations"] and np.array_equal(st.labels(), o["labels"])
+
+
+def test_kmeanspp_edge_cases(km):
+    # every point on one spot: all distances 0 -> the uniform fallback draw
+    x = np.ones((10, 2), dtype=np.float32)
+    with km.KMeansState() as st:
+        st.upload_points(x)
+        st.init_kmeanspp(4, 5)
+        assert np.array_equal(st.centroids(), oracle.kmeanspp_init(x, 4, 5))
+    # after the store was cell-sorted the draw still walks the caller's row order
+    x = oracle.gen_blobs(8, 40000, 2, 32)
+    with km.KMeansState(prune_min_points=1) as st:
+        st.upload_points(x)
+        st.init_forgy(32, 1)
+        st.run(10)                       # sorts the store
+        st.init_kmeanspp(32, 9)
+        assert np.array_equal(st.centroids(), oracle.kmeanspp_init(x, 32, 9))
+        assert np.array_equal(st.get_points(), x)
+        s = st.run(40)
+        o = oracle.run(x, oracle.kmeanspp_init(x, 32, 9), max_iter=40)
+        assert s["iterations"] == o["iterations"] and np.array_equal(st.labels(), o["labels"])
+    st = km.init(x[:5000], 8, seed=3, method="kmeans++")
+    assert np.array_equal(st.centroids(), oracle.kmeanspp_init(x[:5000], 8, 3))
+    with pytest.raises(km.KMeansError):
+        st.init_kmeanspp(0, 1)
+    st.close()
+
+
+@pytest.mark.parametrize("shape", [(20000, 2, 8, {}), (6000, 5, 12, {}), (4000, 32, 16, {}), (40000, 2, 64, {"prune_min_points": 1})],
+                         ids=lambda s: "n%d_d%d_k%d" % s[:3])
+def test_cluster_inertia_and_snapshot_deltas(km, shape):
+    """f2: per-cluster inertia (the numeric stand-in for the dashboard's cohesion) and the
+    snapshot / delta pair of app.mjs:481-521."""
+    n, d, k, kw = shape
+    x = oracle.gen_blobs(70 + d, n, d, k)
+    c0 = oracle.forgy_init(x, k, 4)
+    with km.KMeansState(**kw) as st:
+        st.upload_points(x)
+        st.set_centroids(c0)
+        s1 = st.assign()
+        snap1 = st.snapshot()
+        lab1, _, _ = oracle.assign(x, c0)
+        assert np.allclose(snap1["inertia"], oracle.cluster_inertia(x, lab1, c0), rtol=1e-10, atol=0)
+        assert snap1["total_inertia"] == pytest.approx(s1["inertia"], rel=1e-12)
+        assert snap1["balance"] == oracle.balance(snap1["counts"])
+        s = st.run(40)   # (sorts the store where the pruned path is on)
+        snap2 = st.snapshot()
+        o = oracle.run(x, c0, max_iter=40)
+        assert np.allclose(snap2["inertia"], oracle.cluster_inertia(x, o["labels"], o["centroids"]), rtol=1e-10, atol=0)
+        assert snap2["total_inertia"] == pytest.approx(s["inertia"], rel=1e-12)
+        dl = st.deltas(snap1, snap2)
+        assert dl["gap"] == snap2["balance"]["gap"] - snap1["balance"]["gap"]
+        assert dl["avg_inertia"] <= 0.0 and int(dl["counts"].sum()) == 0   # Lloyd never loosens the fit
+    with km.KMeansState() as st:
+        st.upload_points(x)
+        st.set_centroids(c0)
+        with pytest.raises(km.KMeansError):
+            st.cluster_inertia()   # nothing assigned yet
+
+
 def test_board_export_import_round_trip(km):
     """f3: a finished run written in the demo's {cards, centroids, meta} schema and read back."""
     x = oracle.gen_blobs(6, 300, 2, 3)

@@ -39,6 +39,7 @@ def test_generator_and_forgy_match_golden(path):
     assert np.array_equal(oracle.gen_blobs(int(g["seed"]), n, d, int(g["k_true"])), g["x"])
     k = g["c0"].shape[0]
     assert np.array_equal(oracle.forgy_indices(n, k, int(g["init_seed"])), g["forgy_idx"])
+    assert np.array_equal(oracle.kmeanspp_indices(g["x"], k, int(g["init_seed"])), g["kpp_idx"])
     # a slice generated from the middle equals the same rows of the whole
     assert np.array_equal(oracle.gen_blobs(int(g["seed"]), 50, d, int(g["k_true"]), i0=100), g["x"][100:150])
 
@@ -140,3 +141,28 @@ def test_balance_formulas():
     assert oracle.balance([5, 0, 2])["ratio"] == np.inf
     assert oracle.balance([0, 0])["ratio"] == 1.0
     assert oracle.balance([6, 3]) == dict(max=6, min=3, gap=3, ratio=2.0)
+
+
+def test_kmeanspp_matches_independent_numpy_statement():
+    """A7b: the C oracle's seeded k-means++ against arbitrary-precision Python integers."""
+    from oracle import numpy_ref as nr
+    for (n, d, k, seed) in [(500, 2, 8, 1), (300, 5, 20, 7), (64, 1, 64, 3), (400, 3, 5, 11)]:
+        x = oracle.gen_blobs(seed, n, d, max(2, k // 2))
+        got = oracle.kmeanspp_indices(x, k, seed)
+        assert np.array_equal(got, nr.kmeanspp_indices(x, k, seed))
+        assert len(set(got.tolist())) == k          # distinct points: a chosen row has D = 0 and cannot be drawn again
+    x = np.ones((10, 2), np.float32)                # all distances zero -> uniform fallback
+    assert np.array_equal(oracle.kmeanspp_indices(x, 4, 5), nr.kmeanspp_indices(x, 4, 5))
+    with pytest.raises(ValueError):
+        oracle.kmeanspp_indices(x, 11, 1)
+
+
+def test_cluster_inertia_sums_to_inertia():
+    x = oracle.gen_blobs(9, 3000, 3, 6)
+    c0 = oracle.forgy_init(x, 6, 2)
+    r = oracle.run(x, c0, max_iter=50)
+    ci = oracle.cluster_inertia(x, r["labels"], r["centroids"])
+    assert ci.shape == (6,) and ci.sum() == pytest.approx(r["inertia"], rel=1e-12)
+    d = nr.distances(x, r["centroids"])
+    want = np.array([d[r["labels"] == j, j].sum() for j in range(6)])
+    assert np.allclose(ci, want, rtol=1e-12)
