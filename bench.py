@@ -180,7 +180,7 @@ def run_reference(args, wl):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -383,7 +383,7 @@ def run_ours(args, wl):
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "step_ms_min_med_max": [min(step_ms), statistics.median(step_ms), max(step_ms)],
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     st.close()
     if world > 1:
         dist.destroy_process_group()
@@ -407,7 +407,26 @@ def main():
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     wl = WORKLOADS[args.workload]
+    # stdout carries exactly ONE line, the JSON: anything a library writes to file descriptor 1
+    # meanwhile (NCCL's version banner, for one) is sent to stderr instead
+    sys.stdout.flush()
+    global _JSON_FD
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     return run_reference(args, wl) if args.impl == "reference" else run_ours(args, wl)
+
+
+_JSON_FD = None
+
+
+def emit(line):
+    """Write the bench line to the process's original stdout."""
+    text = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(text.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, text)
 
 
 if __name__ == "__main__":

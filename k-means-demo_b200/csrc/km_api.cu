@@ -1,3 +1,4 @@
+#include <chrono>
 // km_api.cu — the C ABI of libkmeans.so (include/kmeans.h): context, point/centroid
 // store, Lloyd driver loop, NCCL plumbing.  No CPU fallback anywhere: every compute
 // entry point enqueues CUDA kernels or fails.
@@ -176,17 +177,39 @@ static km_status copy_d2h(km_ctx *ctx, void *dst, const void *src, size_t bytes)
     KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return KM_OK;
   }
+  // pageable destination: two pinned halves, the copy of chunk i+1 flies while chunk i is
+  // memcpy'd out of the staging buffer
   const size_t chunk = 32u << 20;
   km_status s = ensure_pinned(ctx, 2 * chunk);
   if (s != KM_OK) return s;
-  size_t off = 0;
-  while (off < bytes) {
-    size_t len = std::min(chunk, bytes - off);
-    KM_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, (const char *)src + off, len, cudaMemcpyDeviceToHost, ctx->stream));
-    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    memcpy((char *)dst + off, ctx->pinned, len);
-    off += len;
+  cudaEvent_t done[2];
+  KM_CUDA(ctx, cudaEventCreateWithFlags(&done[0], cudaEventDisableTiming));
+  KM_CUDA(ctx, cudaEventCreateWithFlags(&done[1], cudaEventDisableTiming));
+  cudaError_t e = cudaSuccess;
+  size_t issued = 0, drained = 0;
+  int slot_issue = 0, slot_drain = 0;
+  size_t len_of[2] = {0, 0};
+  while (drained < bytes && e == cudaSuccess) {
+    while (issued < bytes && issued - drained < 2 * chunk && e == cudaSuccess) {
+      const size_t len = std::min(chunk, bytes - issued);
+      e = cudaMemcpyAsync((char *)ctx->pinned + (size_t)slot_issue * chunk, (const char *)src + issued, len,
+                          cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaEventRecord(done[slot_issue], ctx->stream);
+      len_of[slot_issue] = len;
+      issued += len;
+      slot_issue ^= 1;
+    }
+    if (e != cudaSuccess) break;
+    e = cudaEventSynchronize(done[slot_drain]);
+    if (e != cudaSuccess) break;
+    memcpy((char *)dst + drained, (const char *)ctx->pinned + (size_t)slot_drain * chunk, len_of[slot_drain]);
+    drained += len_of[slot_drain];
+    slot_drain ^= 1;
   }
+  if (e != cudaSuccess) cudaStreamSynchronize(ctx->stream);
+  cudaEventDestroy(done[0]);
+  cudaEventDestroy(done[1]);
+  KM_CUDA(ctx, e);
   return KM_OK;
 }
 
@@ -844,7 +867,13 @@ static km_status maybe_sort_points(km_ctx *ctx) {
   memset(&pr, 0, sizeof(pr));
   if (!km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &pr)) return KM_OK;
   float *x = (float *)ctx->x;
+  static const bool timing = getenv("KM_SORT_TIMING") != nullptr;   // development aid: host wall time of the re-ordering
+  std::chrono::steady_clock::time_point t0;
+  if (timing) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); }
   KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
+  if (timing)
+    fprintf(stderr, "[libkmeans] cell sort of %lld points: %.2f ms\n", (long long)ctx->n,
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
   ctx->x = x;
   ctx->sort_pr = pr;
   return KM_OK;

@@ -4,31 +4,45 @@
 // point falls in.  If consecutive points fall in unrelated cells (the order they were
 // uploaded in), the 32 lanes of a warp walk 32 different lists and the warp runs to its
 // slowest lane.  Points never move during a run, so the store sorts them by cell ONCE (stable
-// radix sort of (cell, original index) — deterministic), keeps the permutation, and
+// radix sort keyed by cell — deterministic), keeps the permutation, and
 // un-permutes labels / rows whenever the caller asks for them.  Every per-cluster sum is
 // order-free, so the results do not depend on this order.
 #include <cub/device/device_radix_sort.cuh>
 
 #include "km_internal.h"
 
-__global__ void __launch_bounds__(256) km_cell_key_kernel(const float2 *__restrict__ x, int64_t n, KmPrune2 pr,
-                                                          unsigned *__restrict__ key, unsigned *__restrict__ idx) {
+// What travels through the radix sort with each cell key: the point itself, its original row and
+// its label — 16 bytes, so the passes move every record with one coalesced 16-byte access and no
+// random gather is needed afterwards (a gather of 8-byte points by a random permutation fetches
+// a 32-byte sector per point: it cost more than the sort itself).
+struct __align__(16) KmSortRec {
+  float x, y;
+  unsigned row;
+  int label;
+};
+
+__global__ void __launch_bounds__(256) km_sort_pack_kernel(const float2 *__restrict__ x, const int32_t *__restrict__ labels,
+                                                           int64_t n, KmPrune2 pr, unsigned *__restrict__ key,
+                                                           KmSortRec *__restrict__ rec) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float2 v = x[i];
     const int ix = min(__float_as_int(fmaf(v.x, pr.sx, pr.kxm)) & 0x3FFFFF, pr.gp - 1);
     const int iy = min(__float_as_int(fmaf(v.y, pr.sy, pr.kym)) & 0x3FFFFF, pr.gp - 1);
     key[i] = (unsigned)(iy * pr.gp + ix);
-    idx[i] = (unsigned)i;
+    KmSortRec r;
+    r.x = v.x; r.y = v.y; r.row = (unsigned)i; r.label = labels[i];
+    rec[i] = r;
   }
 }
 
-__global__ void __launch_bounds__(256) km_gather_kernel(const float2 *__restrict__ x, const int32_t *__restrict__ labels,
-                                                        const unsigned *__restrict__ perm, int64_t n,
-                                                        float2 *__restrict__ xs, int32_t *__restrict__ ls) {
+__global__ void __launch_bounds__(256) km_sort_unpack_kernel(const KmSortRec *__restrict__ rec, int64_t n,
+                                                             float2 *__restrict__ xs, int32_t *__restrict__ ls,
+                                                             unsigned *__restrict__ perm) {
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
-    const unsigned j = perm[p];
-    xs[p] = x[j];
-    ls[p] = labels[j];
+    const KmSortRec r = rec[p];
+    xs[p] = make_float2(r.x, r.y);
+    ls[p] = r.label;
+    perm[p] = r.row;
   }
 }
 
@@ -49,53 +63,41 @@ static int grid_for(int64_t n, int sm_count) {
 }
 
 // Sort the ctx-owned d = 2 points (and their labels) by grid cell.  On success *x and *labels
-// point to new buffers (the old ones are freed) and *perm_out maps sorted position -> original row.
+// hold the sorted rows (same buffers, rewritten) and *perm_out maps sorted position -> original row.
 cudaError_t km_sort_points_by_cell(float **x, int32_t **labels, int64_t n, const KmPrune2 &pr, unsigned **perm_out,
                                    int sm_count, cudaStream_t s, int64_t *launches) {
   *perm_out = nullptr;
   if (n < 2 || n >= ((int64_t)1 << 31)) return cudaSuccess;
-  unsigned *key_in = nullptr, *key_out = nullptr, *idx_in = nullptr, *idx_out = nullptr;
-  void *temp = nullptr;
-  float2 *xs = nullptr;
-  int32_t *ls = nullptr;
-  size_t temp_bytes = 0;
-  cudaError_t e = cudaSuccess;
-  auto cleanup = [&]() {
-    if (key_in) cudaFree(key_in);
-    if (key_out) cudaFree(key_out);
-    if (idx_in) cudaFree(idx_in);
-    if (temp) cudaFree(temp);
-  };
+  // one allocation for everything temporary: keys in/out, records in/out, CUB's scratch
   int bits = 1;
   while ((1 << bits) < pr.gp * pr.gp) bits++;
-  if ((e = cudaMalloc(&key_in, n * sizeof(unsigned))) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&key_out, n * sizeof(unsigned))) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&idx_in, n * sizeof(unsigned))) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&idx_out, n * sizeof(unsigned))) != cudaSuccess) goto fail;
-  km_cell_key_kernel<<<grid_for(n, sm_count), 256, 0, s>>>(reinterpret_cast<const float2 *>(*x), n, pr, key_in, idx_in);
+  size_t temp_bytes = 0;
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (const unsigned *)nullptr, (unsigned *)nullptr,
+                                                  (const KmSortRec *)nullptr, (KmSortRec *)nullptr, (int)n, 0, bits, s);
+  if (e != cudaSuccess) return e;
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const size_t kb = up((size_t)n * sizeof(unsigned)), rb = up((size_t)n * sizeof(KmSortRec));
+  char *pool = nullptr;
+  unsigned *perm = nullptr;
+  if ((e = cudaMalloc(&pool, 2 * kb + 2 * rb + up(temp_bytes))) != cudaSuccess) return e;
+  if ((e = cudaMalloc(&perm, (size_t)n * sizeof(unsigned))) != cudaSuccess) { cudaFree(pool); return e; }
+  unsigned *key_in = reinterpret_cast<unsigned *>(pool), *key_out = reinterpret_cast<unsigned *>(pool + kb);
+  KmSortRec *rec_in = reinterpret_cast<KmSortRec *>(pool + 2 * kb), *rec_out = reinterpret_cast<KmSortRec *>(pool + 2 * kb + rb);
+  void *temp = pool + 2 * kb + 2 * rb;
+  km_sort_pack_kernel<<<grid_for(n, sm_count), 256, 0, s>>>(reinterpret_cast<const float2 *>(*x), *labels, n, pr, key_in, rec_in);
   (*launches)++;
-  if ((e = cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, key_in, key_out, idx_in, idx_out, (int)n, 0, bits, s)) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&temp, temp_bytes)) != cudaSuccess) goto fail;
-  if ((e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, key_in, key_out, idx_in, idx_out, (int)n, 0, bits, s)) != cudaSuccess) goto fail;
+  e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, key_in, key_out, rec_in, rec_out, (int)n, 0, bits, s);   // stable
   (*launches) += 4;
-  if ((e = cudaMalloc(&xs, n * sizeof(float2))) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&ls, n * sizeof(int32_t))) != cudaSuccess) goto fail;
-  km_gather_kernel<<<grid_for(n, sm_count), 256, 0, s>>>(reinterpret_cast<const float2 *>(*x), *labels, idx_out, n, xs, ls);
-  (*launches)++;
-  if ((e = cudaStreamSynchronize(s)) != cudaSuccess) goto fail;
-  cudaFree(*x);
-  cudaFree(*labels);
-  *x = reinterpret_cast<float *>(xs);
-  *labels = ls;
-  *perm_out = idx_out;
-  cleanup();
+  if (e == cudaSuccess) {
+    km_sort_unpack_kernel<<<grid_for(n, sm_count), 256, 0, s>>>(rec_out, n, reinterpret_cast<float2 *>(*x), *labels, perm);
+    (*launches)++;
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  cudaFree(pool);
+  if (e != cudaSuccess) { cudaFree(perm); return e; }
+  *perm_out = perm;
   return cudaSuccess;
-fail:
-  cleanup();
-  if (idx_out) cudaFree(idx_out);
-  if (xs) cudaFree(xs);
-  if (ls) cudaFree(ls);
-  return e;
 }
 
 cudaError_t km_unpermute_labels(const int32_t *labels_sorted, const unsigned *perm, int64_t n, int32_t *out_dev,
