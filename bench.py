@@ -36,6 +36,10 @@ UNIT = "point-iterations/s"
 
 # per-GPU shard shapes (weak scaling).  c5/c4 are the per-GPU shards of configs[4]/[3].
 WORKLOADS = {
+    # configs[0] names a demo workload the reference does not have: the stand-in is
+    # the reference's own card count x 1000 and its maximum k (app.mjs:127, 188, 204-216)
+    "c1": dict(n=12_000, d=2, k=3, k_true=3, seed=1, init_seed=1,
+               name="configs[0] stand-in: N=12000 d=2 k=3 blobs (not present in the reference)"),
     "c2": dict(n=1_000_000, d=2, k=8, k_true=8, seed=2, init_seed=2,
                name="configs[1]: N=1e6 d=2 k=8 blobs per GPU"),
     "c3": dict(n=10_000_000, d=32, k=256, k_true=256, seed=3, init_seed=3,
@@ -129,18 +133,19 @@ def env_rank():
 
 
 # ------------------------------------------------------------------------------- CPU arms
-def cpu_steps(wl, n_sample, steps, warmup, budget_s=None):
-    """Lloyd iterations of the oracle port on all host threads; returns (pt-it/s, steps done,
-    threads).  Same seeded generator and Forgy init as the GPU arm."""
+def cpu_steps(wl, n_sample, steps, warmup, budget_s=None, single_thread=False):
+    """Lloyd iterations of the oracle port on all host threads (or one: the stand-in for a
+    single-threaded JS host); returns (pt-it/s, steps done, threads).  Same seeded generator and
+    Forgy init as the GPU arm."""
     import oracle
     x = oracle.gen_blobs(wl["seed"], n_sample, wl["d"], wl["k_true"])
     c = oracle.forgy_init(x, wl["k"], wl["init_seed"])
     labels = None
-    nthreads = oracle.num_threads()
+    nthreads = 1 if single_thread else oracle.num_threads()
 
     def one():
         nonlocal labels, c
-        labels, changed, _ = oracle.assign(x, c, labels, nthreads=0)
+        labels, changed, _ = oracle.assign(x, c, labels, nthreads=1 if single_thread else 0)
         if changed:
             c, _ = oracle.update(x, labels, c)
 
@@ -367,6 +372,10 @@ def run_ours(args, wl):
         v, done, nthreads, el = cpu_steps(wl, n_sample, 0, 1, budget_s=args.cpu_seconds)
         cpu = {"value": v, "unit": UNIT, "cores": nthreads, "kind": "port",
                "sample": f"{n_sample} points x {done} Lloyd iterations in {el:.1f} s, oracle/kmeans_oracle.c with OpenMP"}
+        # one thread: what a single-threaded JS host (the reference's world) would have to work with
+        n1 = max(50_000, n_sample // max(1, nthreads))
+        v1, done1, _, el1 = cpu_steps(wl, n1, 0, 1, budget_s=min(3.0, args.cpu_seconds), single_thread=True)
+        cpu["single_thread"] = {"value": v1, "sample": f"{n1} points x {done1} Lloyd iterations in {el1:.1f} s, 1 thread"}
 
     if rank == 0:
         line = {
