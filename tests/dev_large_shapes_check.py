@@ -1,7 +1,12 @@
-"""Development check of the small-d kernel's shared-memory ring: shapes that need refills."""
+"""Development check (run by hand on a GPU box, not collected by pytest): multi-million-point
+shapes of every small-d kernel variant against the oracle — many rounds per block, the
+cell-sorted store, the caller-order grid on a borrowed buffer.
+
+    python tests/dev_large_shapes_check.py [all|noprune|d3|grid|unsorted]
+"""
 import sys, time
 import numpy as np
-sys.path.insert(0, ".")
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import kmeans_b200 as km
 import oracle
 
