@@ -469,6 +469,30 @@ def test_large_properties_d2_k64(km):
         assert np.array_equal(lab, olab)
 
 
+@pytest.mark.parametrize("case", ["k8_d2", "k5_d3", "grid_on_borrowed_buffer"])
+def test_many_rounds_per_block(km, case):
+    """Shapes large enough that every block walks several rounds (the software pipeline, ragged last
+    rounds of the last blocks) in the kernel variants the small tests reach with one round."""
+    if case == "grid_on_borrowed_buffer":
+        import torch
+        x = oracle.gen_blobs(3, 6_000_000, 2, 64)
+        c0 = oracle.forgy_init(x, 64, 4)
+        xt = torch.from_numpy(x).cuda()
+        with km.KMeansState(prune_min_points=1) as st:
+            st.attach_points(xt.data_ptr(), x.shape[0], 2)   # borrowed: never re-ordered -> grid over caller order
+            st.set_centroids(c0)
+            s = st.run(5)
+            lab = st.labels()
+    else:
+        n, d, k = (4_000_001, 2, 8) if case == "k8_d2" else (3_000_003, 3, 5)
+        x = oracle.gen_blobs(3, n, d, k)
+        c0 = oracle.forgy_init(x, k, 4)
+        g = gpu_run(km, x, c0, 5)
+        s, lab = g, g["labels"]
+    o = oracle.run(x, c0, max_iter=5, nthreads=0)
+    assert s["iterations"] == o["iterations"] and np.array_equal(lab, o["labels"])
+
+
 # ---------------------------------------------------------------- d = 2 candidate-grid pruning
 def pruned_run(km, x, c0, max_iter=60, update_mode=0):
     return gpu_run(km, x, c0, max_iter, "auto", update_mode, prune_min_points=1)
