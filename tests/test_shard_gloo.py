@@ -86,6 +86,82 @@ def test_two_ranks_reproduce_one_rank_bit_for_bit(tmp_path, n, d, k):
     assert np.array_equal(labels, seq["labels"]) and seq["iterations"] == ref["iterations"]
 
 
+def _kpp_worker(rank, world, port, n, d, k, seed, out_dir):
+    """The sharded k-means++ draw as km_init_kmeanspp does it: per-rank integer totals of the
+    quantised D^2, one all-reduce of the list of totals, the owner rank walks its own prefix."""
+    import math
+    sys.path.insert(0, ROOT)
+    import kmeans_b200 as km
+    import oracle
+    from oracle import numpy_ref as nr
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = km.shard_range(n, rank, world)
+    x = oracle.gen_blobs(seed, hi - lo, d, max(2, k // 2), i0=lo).astype(np.float64)
+    m = torch.tensor([float(np.max(np.abs(x)))], dtype=torch.float64)
+    dist.all_reduce(m, op=dist.ReduceOp.MAX)
+    E = math.frexp(float(m.item()))[1] if m.item() > 0 else 0
+    qd = 62 - max(1, int(n).bit_length()) - (2 * E + 2 + int(d).bit_length())
+    D = np.full(hi - lo, np.inf)
+    state, picks, centre = 21, [], None
+    for s_ in range(k):
+        r = nr.splitmix64(state)
+        state = (state + nr.GAMMA) & nr.MASK
+        u = float(r >> 11) * 2.0 ** -53
+        local = -1
+        by_index = s_ == 0
+        if s_ > 0:
+            D = np.minimum(D, nr.distances(x, centre[None, :])[:, 0])
+            q = [int(math.ldexp(float(v), qd)) for v in D]
+            totals = torch.zeros(world, dtype=torch.int64)
+            totals[rank] = sum(q)
+            dist.all_reduce(totals, op=dist.ReduceOp.SUM)   # every rank fills its own slot
+            tot = [int(v) for v in totals]
+            if sum(tot) == 0:
+                by_index = True
+            else:
+                target = ((r >> 11) * sum(tot)) >> 53
+                owner = world - 1
+                for rk in range(world):
+                    if target < tot[rk]:
+                        owner = rk
+                        break
+                    target -= tot[rk]
+                if owner == rank:
+                    run = 0
+                    local = len(q) - 1
+                    for i, v in enumerate(q):
+                        run += v
+                        if run > target:
+                            local = i
+                            break
+        if by_index:
+            g = int(math.floor(u * float(n)))
+            if lo <= g < hi:
+                local = g - lo
+        row = torch.zeros(d + 1, dtype=torch.float64)        # the row and its global index; zeros elsewhere
+        if local >= 0:
+            row[:d] = torch.from_numpy(x[local])
+            row[d] = float(lo + local)
+        dist.all_reduce(row, op=dist.ReduceOp.SUM)
+        centre = row[:d].numpy().copy()
+        picks.append(int(row[d].item()))
+    np.save(os.path.join(out_dir, f"kpp{rank}.npy"), np.array(picks, dtype=np.int64))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,d,k", [(1201, 2, 9), (700, 3, 16)])
+def test_two_ranks_draw_the_single_rank_kmeanspp_rows(tmp_path, n, d, k):
+    import oracle
+    world, seed = 2, 17
+    mp.spawn(_kpp_worker, args=(world, _free_port(), n, d, k, seed, str(tmp_path)), nprocs=world, join=True)
+    x = oracle.gen_blobs(seed, n, d, max(2, k // 2))
+    want = oracle.kmeanspp_indices(x, k, 21)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / f"kpp{r}.npy"), want)
+
+
 def test_unique_id_needs_nccl_only_when_asked(km):
     # loading the library and the binding must not require NCCL or a GPU
     lib = km._lib.load()
