@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define KM_ABI_VERSION 3
+#define KM_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define KM_API __attribute__((visibility("default")))
@@ -158,8 +158,17 @@ KM_API km_status km_stats_fetch(km_ctx *ctx, km_stats *stats);
 KM_API km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats);
 /* forget labels and sums (the next assign sees every label as changed) */
 KM_API km_status km_reset_labels(km_ctx *ctx);
+/* switch km_config.update_mode for the iterations that follow; labels and sums are reset, as
+ * by km_reset_labels (the two modes keep different things in the tables).  No counterpart in
+ * the reference: both modes produce the same bits, the switch exists to measure one against
+ * the other on resident points. */
+KM_API km_status km_set_update_mode(km_ctx *ctx, int32_t update_mode);
 
 /* ---- results ----------------------------------------------------------------------- */
+/* sizes a binding needs to check a caller's output buffers before the copies below write into
+ * them: rows of this rank's shard, rows of the whole job, d, k (0 while not yet known; any
+ * pointer may be NULL).  No counterpart in the reference. */
+KM_API km_status km_get_shape(const km_ctx *ctx, int64_t *n_local, int64_t *n_total, int32_t *d, int32_t *k);
 KM_API km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n);   /* this rank's shard */
 KM_API km_status km_get_centroids(km_ctx *ctx, double *out);            /* k*d, row-major */
 /* a6: per-cluster member counts of the whole job (analog: snapshotMetrics counts
@@ -194,12 +203,17 @@ KM_API km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t para
  * and it is shared by every call on that GPU — the call clears what it needs first, and two
  * calls whose GPU work overlaps would corrupt each other, so issue them one after another.
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress);
- * make that first call before any stream capture.  Calls no allocating routine. */
+ * make that first call before any stream capture.  Calls no allocating routine.  The first
+ * call on a device is also when the CUDA runtime itself may still allocate (primary context,
+ * lazy loading of this library's kernels and of the array): a host with a no-allocation phase
+ * makes one warm-up call per device at start-up and enters that phase afterwards.  Runs on
+ * `device` and leaves the caller's current device as it found it.  result->status is
+ * KM_ERR_NONFINITE when a point or a centroid was NaN/Inf. */
 typedef struct km_noalloc_result {
   int64_t changed;  /* labels this call changed */
   double inertia;   /* sum of winner distances */
   int64_t n;
-  int32_t status;   /* KM_OK, or KM_ERR_NONFINITE if a point was NaN/Inf (outputs then undefined) */
+  int32_t status;   /* KM_OK, or KM_ERR_NONFINITE if a point or centroid was NaN/Inf (outputs then undefined) */
   int32_t pad;
 } km_noalloc_result;
 KM_API km_status km_lloyd_step_noalloc(int32_t device, void *stream, const float *x, int64_t n, int32_t d,

@@ -14,7 +14,7 @@ ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_OOM, ERR_STATE, ERR_NONFINITE, ERR_UNSU
 DTYPE_F32, DTYPE_F64 = 0, 1
 PATH_AUTO, PATH_DIRECT_F64, PATH_FILTER_F32, PATH_TENSOR = 0, 1, 2, 3
 UPDATE_INCREMENTAL, UPDATE_FULL = 0, 1
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class Config(C.Structure):
@@ -62,6 +62,8 @@ PROTOTYPES = {
     "km_stats_fetch": (_i32, [_vp, C.POINTER(Stats)]),
     "km_run": (_i32, [_vp, _i32, C.POINTER(Stats)]),
     "km_reset_labels": (_i32, [_vp]),
+    "km_set_update_mode": (_i32, [_vp, _i32]),
+    "km_get_shape": (_i32, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i32), C.POINTER(_i32)]),
     "km_get_labels": (_i32, [_vp, _vp, _i64]),
     "km_get_centroids": (_i32, [_vp, _vp]),
     "km_get_counts": (_i32, [_vp, _vp]),

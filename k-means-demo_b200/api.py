@@ -118,9 +118,19 @@ class KMeansState:
         self._check(self._lib.km_generate_blobs(self._h, n, i0, d, k_true, seed, float(sigma)))
         self.n, self.d, self.dtype = n, d, np.dtype(np.float32)
 
-    def get_points(self, i0=0, n=None):
+    @staticmethod
+    def _check_out(out, count, dtype, what):
+        """A caller-supplied result buffer must be exactly what the C call will write."""
+        if not isinstance(out, np.ndarray) or out.dtype != np.dtype(dtype) or not out.flags["C_CONTIGUOUS"] \
+                or out.size != count or not out.flags["WRITEABLE"]:
+            raise ValueError(f"{what}: out must be a writable C-contiguous {np.dtype(dtype).name} array of {count} elements")
+
+    def get_points(self, i0=0, n=None, out=None):
         n = self.n - i0 if n is None else n
-        out = np.empty((n, self.d), dtype=self.dtype)
+        if out is None:
+            out = np.empty((n, self.d), dtype=self.dtype)
+        else:
+            self._check_out(out, n * self.d, self.dtype, "get_points")
         self._check(self._lib.km_get_points(self._h, _ptr(out), i0, n))
         return out
 
@@ -167,14 +177,24 @@ class KMeansState:
     def reset_labels(self):
         self._check(self._lib.km_reset_labels(self._h))
 
+    def set_update_mode(self, mode):
+        """Switch between UPDATE_INCREMENTAL and UPDATE_FULL (labels and sums start over)."""
+        self._check(self._lib.km_set_update_mode(self._h, mode))
+
     # -- results
     def labels(self, out=None):
-        out = np.empty(self.n, dtype=np.int32) if out is None else out
+        if out is None:
+            out = np.empty(self.n, dtype=np.int32)
+        else:
+            self._check_out(out, self.n, np.int32, "labels")
         self._check(self._lib.km_get_labels(self._h, _ptr(out), self.n))
         return out
 
     def centroids(self, out=None):
-        out = np.empty((self.k, self.d), dtype=np.float64) if out is None else out
+        if out is None:
+            out = np.empty((self.k, self.d), dtype=np.float64)
+        else:
+            self._check_out(out, self.k * self.d, np.float64, "centroids")
         self._check(self._lib.km_get_centroids(self._h, _ptr(out)))
         return out
 

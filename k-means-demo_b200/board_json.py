@@ -11,7 +11,10 @@ Mapping used here (ours — the reference has no numeric points):
   point i      -> card `{id: "p:<i>", title: "#<i>", traits: [repr(x_i0), repr(x_i1), ...],
                    assignedTo: "c:<label>" | null, createdBy: "kmeans_b200"}`;
                    for d == 2 also `meta["pos:p:<i>"] = {x, y}` — the reference's own place for a
-                   card's position on the canvas
+                   card's position: a FRACTION of the drop zone, clamped by the demo to
+                   x in [0.02, 0.92], y in [0.10, 0.92] (`app.mjs:362-367`), so the coordinates are
+                   mapped affinely from the points' bounding box into that box (raw values stay in
+                   `traits`, which is what import reads)
   cluster j    -> centroid `{id: "c:<j>", name: "Centroid <j+1>" (the default of app.mjs:128),
                    color, locked: false, coords: [...], count}`; `coords` and `count` are extra
                    keys the demo ignores
@@ -32,6 +35,21 @@ def _color(j):
     return "hsl(%d, 70%%, 55%%)" % int((j * 137.50776405) % 360)
 
 
+POS_BOX = ((0.02, 0.92), (0.10, 0.92))   # the demo's clamp of a card's position (app.mjs:366-367)
+
+
+def canvas_positions(x):
+    """d == 2 points -> fractions of the drop zone inside the demo's clamp box (bounding box of
+    the points mapped affinely onto it; a degenerate axis sits in the middle)."""
+    x = np.asarray(x, dtype=np.float64)
+    out = np.empty_like(x)
+    for t, (lo, hi) in enumerate(POS_BOX):
+        a, b = float(x[:, t].min()), float(x[:, t].max())
+        out[:, t] = (lo + hi) / 2 if b <= a else lo + (hi - lo) * (x[:, t] - a) / (b - a)
+        out[:, t] = np.clip(out[:, t], lo, hi)
+    return out
+
+
 def export_board(points, labels, centroids, iteration=0, inertia=None, counts=None, mode="kmeans"):
     """Arrays -> the `{cards, centroids, meta}` dict the demo's Import accepts."""
     x = np.asarray(points)
@@ -45,12 +63,15 @@ def export_board(points, labels, centroids, iteration=0, inertia=None, counts=No
     if counts is None:
         counts = np.bincount(lab[lab >= 0], minlength=k)
     cards, meta = [], {"iteration": int(iteration), "mode": mode}
+    pos = None
+    if x.shape[1] == 2 and x.shape[0]:
+        pos = canvas_positions(x)
     for i in range(x.shape[0]):
         cid = "p:%d" % i
         cards.append({"id": cid, "title": "#%d" % i, "traits": [repr(float(v)) for v in x[i]],
                       "assignedTo": None if lab[i] < 0 else "c:%d" % lab[i], "createdBy": CREATED_BY})
-        if x.shape[1] == 2:
-            meta["pos:" + cid] = {"x": float(x[i, 0]), "y": float(x[i, 1])}
+        if pos is not None:
+            meta["pos:" + cid] = {"x": float(pos[i, 0]), "y": float(pos[i, 1])}
     cents = [{"id": "c:%d" % j, "name": "Centroid %d" % (j + 1), "color": _color(j), "locked": False,
               "coords": [float(v) for v in c[j]], "count": int(counts[j])} for j in range(k)]
     meta["kmeans"] = {"d": int(x.shape[1]), "dtype": str(x.dtype), "inertia": None if inertia is None else float(inertia)}

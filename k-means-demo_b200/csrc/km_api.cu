@@ -1,4 +1,3 @@
-#include <chrono>
 // km_api.cu — the C ABI of libkmeans.so (include/kmeans.h): context, point/centroid
 // store, Lloyd driver loop, NCCL plumbing.  No CPU fallback anywhere: every compute
 // entry point enqueues CUDA kernels or fails.
@@ -601,6 +600,12 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
     km_status s = reset_labels(ctx);  // k changed: old labels mean nothing
     if (s != KM_OK) return s;
   }
+  if (ctx->p1) {
+    // merge whatever pass is pending under the old centroids — with the scales that pass was
+    // issued with, i.e. BEFORE the bound below changes — then overwrite them
+    km_status s = p1_flush(ctx, -1, -1);
+    if (s != KM_OK) return s;
+  }
   ctx->use_hilo = false;
   {
     // every centroid an update produces is a mean of points: max(max|x|, max|c0|) bounds max|c|
@@ -609,9 +614,6 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
     ctx->cbound = cb;
   }
   if (ctx->p1) {
-    // merge whatever pass is pending under the old centroids, then overwrite them
-    km_status s = p1_flush(ctx, -1, -1);
-    if (s != KM_OK) return s;
     KM_CUDA(ctx, cudaMemcpyAsync(ctx->p1C[ctx->p1_s], c_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // c_host is borrowed for this call only
     return KM_OK;
@@ -861,19 +863,11 @@ static km_status maybe_sort_points(km_ctx *ctx) {
   if (ctx->perm || !ctx->own_x || ctx->d != 2 || ctx->dtype != KM_DTYPE_F32 || !ctx->have_bbox || ctx->cfg.no_prune ||
       ctx->passes_since_upload < 2 || !ctx->p1)
     return KM_OK;
-  static const bool off = getenv("KM_NO_SORT") != nullptr;
-  if (off) return KM_OK;
   KmPrune2 pr;
   memset(&pr, 0, sizeof(pr));
   if (!km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &pr)) return KM_OK;
   float *x = (float *)ctx->x;
-  static const bool timing = getenv("KM_SORT_TIMING") != nullptr;   // development aid: host wall time of the re-ordering
-  std::chrono::steady_clock::time_point t0;
-  if (timing) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); }
   KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
-  if (timing)
-    fprintf(stderr, "[libkmeans] cell sort of %lld points: %.2f ms\n", (long long)ctx->n,
-            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
   ctx->x = x;
   ctx->sort_pr = pr;
   return KM_OK;
@@ -1086,6 +1080,19 @@ extern "C" km_status km_step(km_ctx *ctx, km_stats *stats) {
   return KM_OK;
 }
 
+extern "C" km_status km_set_update_mode(km_ctx *ctx, int32_t update_mode) {
+  KM_BIND(ctx);
+  if (update_mode != KM_UPDATE_INCREMENTAL && update_mode != KM_UPDATE_FULL)
+    return fail(ctx, KM_ERR_INVALID_ARG, "km_set_update_mode: mode out of range");
+  // the two modes keep different things in the tables: start both from nothing
+  km_status s = p1_flush(ctx, -1, -1);
+  if (s != KM_OK) return s;
+  ctx->cfg.update_mode = update_mode;
+  if (ctx->have_points && (s = reset_labels(ctx)) != KM_OK) return s;
+  KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return KM_OK;
+}
+
 extern "C" km_status km_reset_labels(km_ctx *ctx) {
   KM_BIND(ctx);
   if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
@@ -1264,6 +1271,15 @@ extern "C" km_status km_get_sums(km_ctx *ctx, int64_t *sa, int64_t *sb, int32_t 
   if (sa) for (size_t e = 0; e < kd; e++) sa[e] = h[(size_t)L.sa + e];
   if (sb) for (size_t e = 0; e < kd; e++) sb[e] = h[(size_t)L.sb + e];
   if (params4) { params4[0] = ctx->E; params4[1] = ctx->NB; params4[2] = ctx->QB; params4[3] = ctx->qa; }
+  return KM_OK;
+}
+
+extern "C" km_status km_get_shape(const km_ctx *ctx, int64_t *n_local, int64_t *n_total, int32_t *d, int32_t *k) {
+  if (!ctx) return KM_ERR_INVALID_ARG;
+  if (n_local) *n_local = ctx->have_points ? ctx->n : 0;
+  if (n_total) *n_total = ctx->have_points ? ctx->n_total : 0;
+  if (d) *d = ctx->have_points ? ctx->d : 0;
+  if (k) *k = ctx->have_centroids ? ctx->k : 0;
   return KM_OK;
 }
 

@@ -423,7 +423,10 @@ __global__ void __launch_bounds__(KB_THREADS, 1) km_tensor_coarse_bf16_kernel(co
   const uint32_t idesc = umma_idesc_bf16(KT_M, KT_N);
   const int ntiles = (p.k + KT_N - 1) / KT_N;
   const float cnmax = sqrtf(p.st->cnmax2);
-  const float two_e = 2.0f * (0.011049f * p.xnmax * cnmax) + 1e-6f * (p.xnmax * p.xnmax + p.st->cnmax2);
+  // BF16 keeps 8 significant bits: unit roundoff u = 2^-8 per operand, so a product errs by
+  // (2u + u^2)|x_t c_t| and dist~ = |c|^2 - 2 x.c by E = (2^-6 + 2^-15) sum|x_t c_t| <= (2^-6 + 2^-15)|x||c|
+  // (DESIGN.md §6.7); survivors are kept within 2E of the running minimum.
+  const float two_e = 2.0f * (0.0156556f * p.xnmax * cnmax) + 1e-6f * (p.xnmax * p.xnmax + p.st->cnmax2);
   uint32_t phase[2] = {0, 0};
 
   // x rows -> BF16, swizzled K-major (two tiles); lanes sweep float4 chunks, warps sweep rows

@@ -25,6 +25,12 @@
 // only a handle for the runtime.  The first call on each device (with that device current)
 // asks the runtime for the real device address with cudaGetSymbolAddress and keeps it; later
 // calls reuse it.  Make that first call before starting any stream capture on the device.
+// That first call is also the one place where the CUDA runtime itself may still allocate on
+// the caller's behalf: it may create the device's primary context, and — module loading being
+// lazy in CUDA 12 — it is when this file's kernels and the array are actually placed in device
+// memory.  A host with a no-allocation phase therefore makes one warm-up call per device at
+// start-up (any tiny problem will do) and enters that phase afterwards; from the second call
+// on nothing is allocated by anyone.  The caller's current device is left as it was found.
 #include <math.h>
 #include <mutex>
 #include <string>
@@ -93,7 +99,11 @@ __global__ void __launch_bounds__(256) km_na_setup_kernel(KmNaHeader *hdr, const
                                                           int32_t d, int64_t n) {
   __shared__ double red[8];
   double lmax = 0.0;
-  for (int64_t e = threadIdx.x; e < (int64_t)k * d; e += blockDim.x) lmax = fmax(lmax, fabs(c[e]));
+  for (int64_t e = threadIdx.x; e < (int64_t)k * d; e += blockDim.x) {
+    const double v = fabs(c[e]);
+    if (!(v <= 1.7976931348623157e308)) atomicOr(&hdr->nonfinite, 1);   // NaN / Inf among the centroids (fmax would drop a NaN)
+    else lmax = fmax(lmax, v);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = lmax;
@@ -207,7 +217,17 @@ extern "C" km_status km_lloyd_step_noalloc(int32_t device, void *stream, const f
                        " entries (256 KiB); use the context API for this shape");
   // centroid staging must fit the default 48 KB of shared memory (no attribute calls here)
   if ((size_t)d * sizeof(double) > 40 * 1024) return na_fail(KM_ERR_UNSUPPORTED, "km_lloyd_step_noalloc: d too large for one centroid row in shared memory");
-  KM_NA_CUDA(cudaSetDevice(device));
+  // run on `device`, and hand the caller's current device back on every way out
+  struct DeviceGuard {
+    int prev = -1;
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  } guard;
+  int cur = -1;
+  KM_NA_CUDA(cudaGetDevice(&cur));
+  if (cur != device) {
+    KM_NA_CUDA(cudaSetDevice(device));
+    guard.prev = cur;
+  }
   void *base = nullptr;
   KM_NA_CUDA(na_scratch_address(device, &base));
   cudaStream_t s = (cudaStream_t)stream;

@@ -158,9 +158,18 @@ static napi_value km_copy_out(napi_env env, napi_callback_info info, int what) {
     return NULL;
   }
   km_status st = KM_ERR_INVALID_ARG;
-  if (what == 0 && ty == napi_int32_array) st = km_get_labels(ctx, (int32_t *)out, (int64_t)len);
-  else if (what == 1 && ty == napi_float64_array) st = km_get_centroids(ctx, (double *)out);   /* caller sizes it k*d */
-  else if (what == 2 && ty == napi_bigint64_array) st = km_get_counts(ctx, (int64_t *)out);    /* caller sizes it k */
+  int64_t n_local = 0;
+  int32_t d = 0, k = 0;
+  km_get_shape(ctx, &n_local, NULL, &d, &k);
+  /* the C calls write n, k*d and k elements: a shorter typed array would be written past its end */
+  const size_t need = what == 0 ? (size_t)n_local : what == 1 ? (size_t)k * (size_t)d : (size_t)k;
+  if (len < need) {
+    napi_throw_error(env, "ERR_KMEANS", "output typed array is shorter than the result (labels: n, centroids: k*d, counts: k)");
+    return NULL;
+  }
+  if (what == 0 && ty == napi_int32_array) st = km_get_labels(ctx, (int32_t *)out, n_local);
+  else if (what == 1 && ty == napi_float64_array) st = km_get_centroids(ctx, (double *)out);
+  else if (what == 2 && ty == napi_bigint64_array) st = km_get_counts(ctx, (int64_t *)out);
   else { napi_throw_error(env, "ERR_KMEANS", "output array has the wrong element type"); return NULL; }
   if (st != KM_OK) return km_throw(env, ctx);
   return km_undefined(env);

@@ -32,7 +32,7 @@ def test_schema_is_the_demos():
     assert {"id", "name", "color", "locked"} <= set(b["centroids"][0])                     # app.mjs:128
     assert b["cards"][0]["assignedTo"] == "c:1" and b["cards"][1]["assignedTo"] is None
     assert b["centroids"][1]["name"] == "Centroid 2" and b["centroids"][0]["locked"] is False
-    assert b["meta"]["iteration"] == 3 and b["meta"]["pos:p:0"] == {"x": 0.5, "y": 1.0}   # app.mjs:158, 288
+    assert b["meta"]["iteration"] == 3 and b["meta"]["pos:p:0"] == {"x": 0.02, "y": 0.1}   # app.mjs:158, 288, 366-367
     assert all(isinstance(t, str) for t in b["cards"][0]["traits"])
     assert [c["count"] for c in b["centroids"]] == [0, 1]
 
@@ -55,3 +55,19 @@ def test_bad_input():
         bj.import_board({"cards": 3})
     with pytest.raises(ValueError):
         bj.export_board(np.zeros((2, 2)), [0, 5], np.zeros((2, 2)))
+
+
+def test_exported_positions_lie_in_the_demo_clamp_box():
+    """`pos:<id>` is a fraction of the drop zone which the demo clamps to x in [0.02, 0.92],
+    y in [0.10, 0.92] (/root/reference/app.mjs:362-367): exported cards must land on the canvas."""
+    rng = np.random.default_rng(0)
+    x = (rng.standard_normal((200, 2)) * [50.0, 0.001] + [1000.0, -3.0]).astype(np.float32)
+    lab = rng.integers(0, 3, 200)
+    b = bj.export_board(x, lab, np.zeros((3, 2)))
+    xs = np.array([[b["meta"]["pos:p:%d" % i]["x"], b["meta"]["pos:p:%d" % i]["y"]] for i in range(200)])
+    assert xs[:, 0].min() >= 0.02 and xs[:, 0].max() <= 0.92 and xs[:, 1].min() >= 0.10 and xs[:, 1].max() <= 0.92
+    assert np.argmax(xs[:, 0]) == np.argmax(x[:, 0]) and np.argmin(xs[:, 1]) == np.argmin(x[:, 1])   # order kept
+    back = bj.import_board(bj.loads(bj.dumps(b)))
+    assert np.array_equal(back["points"], x)           # the raw coordinates still round-trip through `traits`
+    one = bj.export_board(x[:1], lab[:1], np.zeros((3, 2)))
+    assert one["meta"]["pos:p:0"] == pytest.approx({"x": 0.47, "y": 0.51})

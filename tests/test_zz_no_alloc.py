@@ -48,8 +48,15 @@ def test_noalloc_step_matches_context_step_twice(km, n, d, k):
         ref.set_centroids(c0)
         c_in, c_out = c_a, c_b
         for call in range(2):                        # two calls in a row share the built-in array
+            torch.cuda.synchronize()
+            free_before = torch.cuda.mem_get_info(dev)[0]
             _call(lib, L, xt, n, d, c_in, k, labels, c_out, counts, res)
             torch.cuda.synchronize()
+            if call == 1:
+                # the property the entry point exists for: past the warm-up call (context and
+                # module set-up), a call leaves the device's free memory exactly where it was
+                assert torch.cuda.mem_get_info(dev)[0] == free_before
+            assert torch.cuda.current_device() == 0
             want = ref.step()
             got = L.NoAllocResult.from_buffer_copy(res.cpu().numpy().tobytes())
             assert got.status == L.OK and got.n == n
@@ -89,3 +96,31 @@ def test_noalloc_rejects_shapes_beyond_the_builtin_array(km):
     st = lib.km_lloyd_step_noalloc(0, None, xt.data_ptr(), n, 0, c.data_ptr(), k, labels.data_ptr(), c.data_ptr(),
                                    counts.data_ptr(), res.data_ptr())
     assert st == L.ERR_INVALID_ARG
+
+
+def test_noalloc_flags_nonfinite_centroids_and_keeps_the_current_device(km):
+    import torch
+    L = km._lib
+    lib = L.load()
+    dev = torch.device("cuda", 0)
+    n, d, k = 256, 2, 3
+    xt = torch.zeros((n, d), dtype=torch.float32, device=dev)
+    c = torch.zeros((k, d), dtype=torch.float64, device=dev)
+    c[1, 0] = float("nan")
+    labels = torch.full((n,), -1, dtype=torch.int32, device=dev)
+    counts = torch.zeros(k, dtype=torch.int64, device=dev)
+    res = torch.zeros(C.sizeof(L.NoAllocResult), dtype=torch.uint8, device=dev)
+    out = torch.empty_like(c)
+    _call(lib, L, xt, n, d, c, k, labels, out, counts, res)
+    torch.cuda.synchronize()
+    got = L.NoAllocResult.from_buffer_copy(res.cpu().numpy().tobytes())
+    assert got.status == L.ERR_NONFINITE
+    if torch.cuda.device_count() > 1:                # a call for another device leaves the caller's device current
+        with torch.cuda.device(1):
+            x1, c1 = xt.to("cuda:1"), torch.zeros((k, d), dtype=torch.float64, device="cuda:1")
+            l1, n1 = labels.to("cuda:1"), counts.to("cuda:1")
+            r1, o1 = res.to("cuda:1"), torch.empty((k, d), dtype=torch.float64, device="cuda:1")
+        st = lib.km_lloyd_step_noalloc(1, None, x1.data_ptr(), n, d, c1.data_ptr(), k, l1.data_ptr(), o1.data_ptr(),
+                                       n1.data_ptr(), r1.data_ptr())
+        assert st == L.OK and torch.cuda.current_device() == 0
+        torch.cuda.synchronize(1)
