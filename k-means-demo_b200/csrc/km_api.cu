@@ -215,14 +215,31 @@ static km_status copy_d2h(km_ctx *ctx, void *dst, const void *src, size_t bytes)
 static int bitlen64(int64_t v) { int b = 1; while (b < 62 && ((int64_t)1 << b) <= v) b++; return b; }
 
 // fixed-point parameters of the order-free sums from the job's max|x| and N
-static km_status push_state(km_ctx *ctx) {
+static int bitlen32(int32_t v) { int b = 0; while ((1 << b) <= v) b++; return b; }
+
+// grids of the order-free sums and of T = sum |x|^2 (§4.1) from the job's max|x| and N
+static void compute_grids(km_ctx *ctx) {
   int E = 0;
   if (ctx->maxabs > 0.0) E = ilogb(ctx->maxabs) + 1;
   int NB = bitlen64(ctx->n_total);
   ctx->E = E; ctx->NB = NB; ctx->QB = 62 - NB; ctx->qa = ctx->QB - E;
+  ctx->QBt = 61 - NB - bitlen32(ctx->d);
+  ctx->qt = std::min(ctx->QBt - 2 * E, 900);
+}
+// grid of the inertia terms c (2S - n c): |c| is bounded by max(max|x|, max|c0|)
+static void inertia_grid(const km_ctx *ctx, int *qg, int *QBg) {
+  const double M = std::max(ctx->cbound, ctx->maxabs);
+  const int EM = M > 0.0 ? ilogb(M) + 1 : 0;
+  *QBg = 60 - ctx->NB - bitlen32(ctx->d);
+  *qg = std::min(*QBg - 2 * EM, 900);
+}
+
+static km_status push_state(km_ctx *ctx) {
+  const int E = ctx->E;
   KmState st;
   memset(&st, 0, sizeof(st));
   st.QB = ctx->QB; st.qa = ctx->qa; st.E = E;
+  st.Ta = ctx->Ta; st.Tb = ctx->Tb; st.qt = ctx->qt; st.QBt = ctx->QBt;
   st.scale_a = ldexp(1.0, ctx->qa);
   st.scale_b = ldexp(1.0, ctx->QB);
   st.qi = ctx->QB;  // refreshed with the centroids
@@ -256,6 +273,7 @@ static KmFinalizeArgs make_fin(km_ctx *ctx, KmStatSlot *slot, int do_stats, int 
   f.c64 = ctx->c64; f.chi = ctx->chi; f.clo = ctx->clo;
   f.k = ctx->k; f.d = ctx->d; f.st = ctx->state; f.slot = slot; f.maxabs_x = ctx->maxabs;
   f.do_stats = do_stats; f.do_update = do_update; f.update_needs_change = needs_change;
+  inertia_grid(ctx, &f.qg, &f.QBg);
   return f;
 }
 
@@ -318,6 +336,18 @@ static km_status adopt_points(km_ctx *ctx) {
   ctx->n_total = n_total;
   ctx->i0 = i0;
   ctx->have_points = true;
+  compute_grids(ctx);
+  {
+    // T = sum |x|^2 over the whole job, once per upload: exact limbs on the grid just fixed
+    KM_CUDA(ctx, km_launch_sumsq(ctx->x, ctx->dtype, ctx->n * (int64_t)ctx->d, ldexp(1.0, ctx->qt), ldexp(1.0, ctx->QBt),
+                                 ctx->scan_t, ctx->sm_count, ctx->stream, &ctx->launches));
+    if (ctx->world > 1)
+      KM_NCCL(ctx, g_nccl.all_reduce(ctx->scan_t, ctx->scan_t, 2, KM_NCCL_INT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream));
+    long long ht[2] = {0, 0};
+    KM_CUDA(ctx, cudaMemcpyAsync(ht, ctx->scan_t, sizeof(ht), cudaMemcpyDeviceToHost, ctx->stream));
+    KM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->Ta = ht[0]; ctx->Tb = ht[1];
+  }
   km_status s = push_state(ctx);
   if (s != KM_OK) return s;
   s = reset_labels(ctx);
@@ -413,6 +443,7 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   KM_CREATE_CUDA(cudaMalloc(&ctx->scan_max, sizeof(double)));
   KM_CREATE_CUDA(cudaMalloc(&ctx->scan_bad, sizeof(int)));
   KM_CREATE_CUDA(cudaMalloc(&ctx->scan_bbox, 4 * sizeof(unsigned)));
+  KM_CREATE_CUDA(cudaMalloc(&ctx->scan_t, 2 * sizeof(long long)));
   for (int q = 0; q < KM_PROF_RING; q++) {
     KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][0]));
     KM_CREATE_CUDA(cudaEventCreate(&ctx->prof_ev[q][1]));
@@ -439,6 +470,7 @@ extern "C" km_status km_destroy(km_ctx *ctx) {
   if (ctx->scan_max) cudaFree(ctx->scan_max);
   if (ctx->scan_bad) cudaFree(ctx->scan_bad);
   if (ctx->scan_bbox) cudaFree(ctx->scan_bbox);
+  if (ctx->scan_t) cudaFree(ctx->scan_t);
   for (int q = 0; q < KM_PROF_RING; q++)
     for (int w = 0; w < 2; w++) if (ctx->prof_ev[q][w]) cudaEventDestroy(ctx->prof_ev[q][w]);
   if (ctx->ring) cudaFreeHost(ctx->ring);
@@ -936,6 +968,8 @@ static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
   ps.apply_update = update;
   ps.needs_change = nc;
   ps.QB = ctx->QB; ps.qa = ctx->qa; ps.maxabs_x = ctx->maxabs;
+  ps.Ta = ctx->Ta; ps.Tb = ctx->Tb; ps.qt = ctx->qt; ps.QBt = ctx->QBt;
+  inertia_grid(ctx, &ps.qg, &ps.QBg);
   const bool prof = assign && ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
   if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
   KM_CUDA(ctx, km_launch_assign_small(a, &ctx->launches));

@@ -20,7 +20,7 @@ km_assign_direct_kernel(const XT *__restrict__ x, int64_t n, int32_t d, int32_t 
   T.L = L;
   T.tab = tab_in_smem ? stab : acc;
   if (tab_in_smem) km_tab_zero(stab, L.scal);
-  const double scale_a = st->scale_a, scale_b = st->scale_b, inertia_scale = st->inertia_scale;
+  const double scale_a = st->scale_a, scale_b = st->scale_b;
   KmThreadScalars S;
   const int64_t ntiles = (n + KM_DIRECT_THREADS - 1) / KM_DIRECT_THREADS;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -44,7 +44,7 @@ km_assign_direct_kernel(const XT *__restrict__ x, int64_t n, int32_t d, int32_t 
     if (live) {
       const int old = labels[i];
       if (lab != old) labels[i] = lab;
-      km_commit_point(T, S, xrow, d, old, lab, best, incremental, scale_a, scale_b, inertia_scale);
+      km_commit_point_sums(T, S, xrow, d, old, lab, incremental, scale_a, scale_b);
     }
   }
   __syncthreads();

@@ -89,8 +89,6 @@ struct KmSmallParams {
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
   int64_t chunk;       // points per chunk (multiple of 4); block b walks chunks b, b + grid, ...
   int64_t nchunks;
-  double inertia_scale;  // 2^qi, from the host-side bound on max|c|
-  int qi;
   float tau2;          // absolute error term of the filter for this instantiation (hi or hi/lo)
   float cboundf;       // the bound on max|c| itself
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
@@ -197,6 +195,30 @@ __device__ __forceinline__ void km_load_labels(KmBatch<D> &b, const int32_t *__r
   }
 }
 
+// Block 0, prologue: the inertia of the pending pass from the sums (km_common.cuh):
+// this warp's share of the terms c (2S - n c) over the merged sums and the centroids that pass
+// used (C_in), left in sg[warp][0..1].  Kept out of line so its double-double arithmetic costs
+// the main loop no registers.
+__device__ __noinline__ void km_small_inertia_terms(const long long *S_in, const long long *D_in, const double *C_in,
+                                                    int full_mode, int k, int D, int QB, int qa, int qg, int QBg,
+                                                    long long (*sg)[2]) {
+  const KmAccLayout L = km_acc_layout(k, D);
+  const double scale_g = scalbn(1.0, qg), scale_gb = scalbn(1.0, QBg);
+  long long ga = 0, gb = 0;
+  for (int e = threadIdx.x; e < k * D; e += KM_SMALL_THREADS) {
+    const int jj = e / D;
+    long long sa = S_in[L.sa + e], sb = S_in[L.sb + e], cn = S_in[L.cnt + jj];
+    const long long da = D_in[L.sa + e], db = D_in[L.sb + e], dc = D_in[L.cnt + jj];
+    if (full_mode) { sa = da; sb = db; cn = dc; } else { sa += da; sb += db; cn += dc; }
+    long long ta, tb;
+    km_inertia_term(C_in[e], sa, sb, cn, QB, qa + QB, scale_g, scale_gb, ta, tb);
+    ga += ta; gb += tb;
+  }
+  ga = km_warp_sum_ll(ga);
+  gb = km_warp_sum_ll(gb);
+  if ((threadIdx.x & 31) == 0) { sg[threadIdx.x >> 5][0] = ga; sg[threadIdx.x >> 5][1] = gb; }
+}
+
 template <int D, bool HILO, bool PRUNE>
 __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
   static_assert(!PRUNE || D == 2, "candidate pruning is built for d == 2");
@@ -239,6 +261,11 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     }
   };
 
+  // block 0 owes the host the pending pass's inertia: its terms first, while no register is live
+  __shared__ long long s_g[KM_SMALL_THREADS / 32][2];   // per-warp shares of those terms
+  if (blockIdx.x == 0 && ps.D_in != nullptr && ps.slot != nullptr)
+    km_small_inertia_terms(ps.S_in, ps.D_in, ps.C_in, ps.full_mode, k, D, ps.QB, ps.qa, ps.qg, ps.QBg, s_g);
+
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
   constexpr bool EARLY_LABELS = !PRUNE;   // see km_load_labels
@@ -275,9 +302,10 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       ps.C_out[e] = c;
     }
   }
-  __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, inertia limbs, rescored
+  __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, rescored
   const int lane = threadIdx.x & 31;
   if (threadIdx.x < KM_ACC_SCALARS) s_scal[threadIdx.x] = 0;
+  const bool publish = blockIdx.x == 0 && pend && ps.slot != nullptr;
   KmBlockTab T;
   T.L = L;
   T.tab = p.tab_in_smem ? stab : ps.D_out;
@@ -285,23 +313,24 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   if (blockIdx.x == 0) {
     if (ps.D_zero)
       for (int e = threadIdx.x; e < (int)L.len; e += KM_SMALL_THREADS) ps.D_zero[e] = 0;
-    if (threadIdx.x == 0 && pend && ps.slot) {
-      KmStatSlot sl;
-      sl.it = ps.it_pending;
-      sl.changed = changed_prev;
-      sl.inertia = km_fixed_to_double(ps.D_in[L.scal + KM_ACC_INERTIA_A], ps.D_in[L.scal + KM_ACC_INERTIA_B], ps.QB,
-                                      p.qi + ps.QB);
-      sl.rescored = ps.D_in[L.scal + KM_ACC_RESCORED];
-      sl.updated = upd ? 1 : 0;
-      sl.pad = 0;
-      *ps.slot = sl;   // pinned host memory; visible once this kernel's event completes
-    }
   }
   __syncthreads();
+  if (publish && threadIdx.x == 0) {
+    long long ga = 0, gb = 0;
+    for (int w = 0; w < KM_SMALL_THREADS / 32; w++) { ga += s_g[w][0]; gb += s_g[w][1]; }
+    KmStatSlot sl;
+    sl.it = ps.it_pending;
+    sl.changed = changed_prev;
+    sl.inertia = km_inertia_from_limbs(ps.Ta, ps.Tb, ps.QBt, ps.qt, ga, gb, ps.QBg, ps.qg);
+    sl.rescored = ps.D_in[L.scal + KM_ACC_RESCORED];
+    sl.updated = upd ? 1 : 0;
+    sl.pad = 0;
+    *ps.slot = sl;   // pinned host memory; visible once this kernel's event completes
+  }
   // The error term of the filter and the inertia scale need max|c|.  Every centroid the
   // update produces is a mean of points, so max(max|x|, max|c0|) — known on the host when the
   // centroids were set — bounds it for every later pass: no reduction, no second barrier.
-  const double scale_a = p.scale_a, scale_b = p.scale_b, inertia_scale = p.inertia_scale;
+  const double scale_a = p.scale_a, scale_b = p.scale_b;
   const float tau2 = p.tau2;   // absolute part of the ambiguity threshold (2.5x margin included)
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
@@ -406,7 +435,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   }
 
   int changed = 0, rescored = 0;
-  double inertia = 0.0;
 
   for (int64_t ch = blockIdx.x; ch < p.nchunks; ch += gridDim.x) {
   const int cn = chunk_len(ch);
@@ -485,7 +513,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       }
       const int n0 = (int)(w0 & 0xFF);
       if (uniform && n0 != 0xFF) {
-        if (n0 == 1 && p.exact_inertia) {
+        if (n0 == 1) {
           // the only candidate wins: key = its index under distance bits 0 ("clear" below)
 #pragma unroll
           for (int q = 0; q < PPT; q++) m1[q] = (unsigned)((w0 >> 8) & 0xFF);
@@ -593,16 +621,11 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       int newlab[PPT];
       bool anypush = false;
       if (PRUNE && FULL && one_candidate) {
-        // whole warp, one candidate: nothing to compare — the winner's exact distance for the
-        // inertia, and a look at the old labels
+        // whole warp, one candidate: nothing to compare, nothing to measure (the inertia comes
+        // from the sums) — only a look at the old labels
         const int lab = (int)m1[0];
-        const double c0 = cd[(size_t)lab * D], c1 = cd[(size_t)lab * D + (D > 1 ? 1 : 0)];
 #pragma unroll
         for (int q = 0; q < PPT; q++) {
-          float x0, x1;
-          unpk2(cur.xq[q][0], x0, x1);
-          const double d0 = __dsub_rn((double)x0, c0), d1 = __dsub_rn((double)x1, c1);
-          inertia += __dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1));   // 0 + a + b == a + b exactly
           newlab[q] = lab;
           const bool moved = lab != cur.old[q];
           changed += moved ? 1 : 0;
@@ -623,20 +646,16 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           // No runner-up at all (k == 1, or a pruned cell with a single candidate) is unambiguous
           // by construction; no winner at all (an overflowed cell) is not.
           const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
-          double best;
           if (live && !clear) {
             rescored++;
-            best = __longlong_as_double(0x7FF0000000000000LL);
+            double best = __longlong_as_double(0x7FF0000000000000LL);
             lab = 0;
             for (int j = 0; j < k; j++) {
               const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
               if (dj < best) { best = dj; lab = j; }
             }
-          } else {
-            best = p.exact_inertia ? km_dist2_f64(xr, cd + (size_t)lab * D, D) : (double)b1;
           }
-          if (!live) { best = 0.0; lab = cur.old[q]; }
-          inertia += best;
+          if (!live) lab = cur.old[q];
           newlab[q] = lab;
           const bool moved = lab != cur.old[q];
           changed += moved ? 1 : 0;
@@ -716,20 +735,12 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
   }
 
-  // ---- block epilogue.  Counts go through one REDUX per warp; the inertia partial is summed
-  // across the warp in binary64 and made order-free there (one split per warp), so every
-  // add beyond this point is an integer add.
+  // ---- block epilogue.  Counts go through one REDUX per warp.
   {
     const int wc = __reduce_add_sync(0xffffffffu, changed), wr = __reduce_add_sync(0xffffffffu, rescored);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) inertia += __shfl_xor_sync(0xffffffffu, inertia, o);
     if (lane == 0) {
-      long long ia, ib;
-      km_fixed_split(inertia, inertia_scale, scale_b, ia, ib);
       if (wc) km_atomic_add_ll(&s_scal[KM_ACC_CHANGED], wc);
       if (wr) km_atomic_add_ll(&s_scal[KM_ACC_RESCORED], wr);
-      km_atomic_add_ll(&s_scal[KM_ACC_INERTIA_A], ia);
-      km_atomic_add_ll(&s_scal[KM_ACC_INERTIA_B], ib);
     }
   }
   __syncthreads();
@@ -810,8 +821,6 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   }
   p.scale_a = a.scale_a;
   p.scale_b = a.scale_b;
-  p.inertia_scale = a.h_inertia_scale;
-  p.qi = a.h_qi;
   p.tau2 = HILO ? a.h_tau_hilo : a.h_tau_hi;
   p.cboundf = (float)a.h_cbound * 1.0000002f;
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);

@@ -663,14 +663,13 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
                         const float *__restrict__ chi, const double *__restrict__ c64, int32_t *__restrict__ labels,
                         long long *__restrict__ acc, const KmState *__restrict__ st, int incremental, int exact_inertia) {
   const KmAccLayout L = km_acc_layout(k, d);
-  const double scale_a = st->scale_a, scale_b = st->scale_b, inertia_scale = st->inertia_scale;
+  const double scale_a = st->scale_a, scale_b = st->scale_b;
   const float tau2 = st->tau_hi;
   const float rho2 = 2.5f * (float)(d + 6) * 0x1.0p-24f;
   const int lane = threadIdx.x & 31, g = lane >> 3, sl = lane & 7;
   const int nq = d >> 5;                                   // float4 slices per lane (1..4)
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   KmThreadScalars S;
-  double inertia = 0.0;
   for (int64_t base = warp0 * 4; base < n; base += nwarps * 4) {
     const int64_t i = base + g;
     const bool live = i < n;
@@ -732,44 +731,7 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
       have_best = true;
     }
     lab = __shfl_sync(0xffffffffu, lab, g * 8);     // the group's lane 0 holds the decision
-    if (exact_inertia) {
-      double part = 0.0;
-      if (live && !have_best) {
-        const double *cr = c64 + (int64_t)lab * d;
-#pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (q < nq) {
-            const double2 c0 = *reinterpret_cast<const double2 *>(cr + (q * 8 + sl) * 4);
-            const double2 c1 = *reinterpret_cast<const double2 *>(cr + (q * 8 + sl) * 4 + 2);
-            double df = __dsub_rn((double)xq[q].x, c0.x); part = __dadd_rn(part, __dmul_rn(df, df));
-            df = __dsub_rn((double)xq[q].y, c0.y); part = __dadd_rn(part, __dmul_rn(df, df));
-            df = __dsub_rn((double)xq[q].z, c1.x); part = __dadd_rn(part, __dmul_rn(df, df));
-            df = __dsub_rn((double)xq[q].w, c1.y); part = __dadd_rn(part, __dmul_rn(df, df));
-          }
-      }
-      part = kt_sum8(part);
-      if (!have_best) best = part;
-    } else if (!have_best) {
-      float part = 0.f;
-      if (live && ncand == 1) {   // no binary32 distance was needed for the decision: take it now
-        const float *cr = chi + (int64_t)lab * d;
-#pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (q < nq) {
-            const float4 cv = *reinterpret_cast<const float4 *>(cr + (q * 8 + sl) * 4);
-            float df = xq[q].x - cv.x; part = fmaf(df, df, part);
-            df = xq[q].y - cv.y; part = fmaf(df, df, part);
-            df = xq[q].z - cv.z; part = fmaf(df, df, part);
-            df = xq[q].w - cv.w; part = fmaf(df, df, part);
-          }
-      }
-      part = kt_sum8(part);
-      best = (live && ncand == 1) ? (double)part : (double)b1;
-    }
-    if (live && sl == 0) {
-      inertia += best;
-      if (lab != old) { S.changed++; labels[i] = lab; }
-    }
+    if (live && sl == 0 && lab != old) { S.changed++; labels[i] = lab; }
     const bool move = live && (incremental ? (lab != old) : true);
     if (move) {
       // consecutive lanes take consecutive dimensions: 8 lanes = 64 contiguous bytes per limb row
@@ -790,7 +752,6 @@ km_tensor_stage2_kernel(const float *__restrict__ x, int64_t n, int d, int k, co
       }
     }
   }
-  km_fixed_split(inertia, inertia_scale, scale_b, S.ia, S.ib);
   km_flush_scalars(S, acc, L);
 }
 

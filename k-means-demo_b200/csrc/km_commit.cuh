@@ -61,6 +61,19 @@ __device__ __forceinline__ void km_commit_point(const KmBlockTab &T, KmThreadSca
   S.ib += b;
 }
 
+// the same without the per-point inertia (the context API takes the inertia from the sums,
+// DESIGN.md §4.1): label compare and the move between the order-free sums
+template <typename XT>
+__device__ __forceinline__ void km_commit_point_sums(const KmBlockTab &T, KmThreadScalars &S, const XT *xrow, int d,
+                                                     int old, int lab, int incremental, double scale_a, double scale_b) {
+  if (lab != old) S.changed++;
+  if (incremental) {
+    if (lab != old) km_move_point(T, xrow, d, lab, old, scale_a, scale_b);
+  } else {
+    km_move_point(T, xrow, d, lab, -1, scale_a, scale_b);
+  }
+}
+
 // block-wide sum of the per-thread scalars, then four global atomics per block
 __device__ __forceinline__ void km_flush_scalars(const KmThreadScalars &S, long long *gacc, const KmAccLayout &L) {
   __shared__ long long red[4][32];

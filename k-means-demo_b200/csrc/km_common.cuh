@@ -51,6 +51,11 @@ struct KmState {
   unsigned long long cmax_bits;  // scratch for the finalize kernel's max reduction
   float cnmax2;          // tensor path: max_j |chi_j|^2 of the current centroids
   float pad0;
+  // inertia from the sums: T = sum_i |x_i|^2 of the whole job as order-free limbs
+  // on the grid 2^-(qt + QBt), and the accumulator of the per-element terms of one finalize
+  long long Ta, Tb;
+  unsigned long long g_a, g_b;
+  int32_t qt, QBt;       // T's grid: QBt = 61 - NB - bitlen(d), qt = QBt - 2E
 };
 
 // Small-d path ("prologue-finalize" protocol): what one pass reads and writes.
@@ -72,6 +77,9 @@ struct KmPass {
   int needs_change;        // ... only if the pending pass changed a label
   int QB, qa;
   double maxabs_x;
+  long long Ta, Tb;        // sum_i |x_i|^2 of the whole job (order-free limbs), for the inertia
+  int qt, QBt;
+  int qg, QBg;             // grid of the inertia terms: QBg = 60 - NB - bitlen(d), qg = QBg - 2 E(max(max|x|, max|c|))
 };
 
 // d == 2 candidate pruning.  A point's cell is RN(x*sx + Kx), RN(y*sy + Ky):
@@ -185,6 +193,81 @@ __device__ __forceinline__ double km_dist2_f64(const XT *__restrict__ xrow, cons
     acc = __dadd_rn(acc, __dmul_rn(df, df));
   }
   return acc;
+}
+
+// ---------------------------------------------------------------------------------
+// Inertia from the sums.  With labels l(i), centroids c and the exact per-cluster sums S_j, n_j:
+//     sum_i |x_i - c_l(i)|^2  =  T  -  sum_{j,t} c_jt (2 S_jt - n_j c_jt),     T = sum_i |x_i|^2
+// an identity of real numbers, so no per-point distance is needed for the total.  T is a
+// constant of the data set (one exact pass at upload), S and n are the order-free sums the update
+// keeps anyway.  Every term is evaluated in double-double arithmetic (~104 bits) and put on the
+// fixed-point grid of T individually, so the result is a sum of integers: identical for any
+// blocking or GPU count, and good to ~2^-100 * T even when T is many orders of magnitude larger
+// than the inertia (data far from the origin).
+// ---------------------------------------------------------------------------------
+struct KmDD { double hi, lo; };
+__device__ __forceinline__ KmDD km_two_sum(double a, double b) {
+  KmDD r;
+  r.hi = __dadd_rn(a, b);
+  const double bb = __dsub_rn(r.hi, a);
+  r.lo = __dadd_rn(__dsub_rn(a, __dsub_rn(r.hi, bb)), __dsub_rn(b, bb));
+  return r;
+}
+__device__ __forceinline__ KmDD km_two_prod(double a, double b) {
+  KmDD r;
+  r.hi = __dmul_rn(a, b);
+  r.lo = __fma_rn(a, b, -r.hi);
+  return r;
+}
+__device__ __forceinline__ KmDD km_dd_add(KmDD a, KmDD b) {
+  KmDD s = km_two_sum(a.hi, b.hi);
+  const KmDD t = km_two_sum(a.lo, b.lo);
+  s.lo = __dadd_rn(s.lo, t.hi);
+  s = km_two_sum(s.hi, s.lo);
+  s.lo = __dadd_rn(s.lo, t.lo);
+  return km_two_sum(s.hi, s.lo);
+}
+__device__ __forceinline__ KmDD km_dd_mul_d(KmDD a, double b) {
+  KmDD p = km_two_prod(a.hi, b);
+  p.lo = __fma_rn(a.lo, b, p.lo);
+  return km_two_sum(p.hi, p.lo);
+}
+// exact value of the limb pair (Sa * 2^QB + Sb) * 2^-shift as a double-double (error < 2^-105 relative)
+__device__ __forceinline__ KmDD km_fixed_to_dd(long long Sa, long long Sb, int QB, int shift) {
+  // four exactly representable pieces: Sa = ah * 2^32 + al, Sb = bh * 2^32 + bl
+  const double ah = (double)(Sa >> 32), al = (double)(unsigned)(Sa & 0xFFFFFFFFLL);
+  const double bh = (double)(Sb >> 32), bl = (double)(unsigned)(Sb & 0xFFFFFFFFLL);
+  KmDD r = km_two_sum(scalbn(ah, 32 + QB - shift), scalbn(al, QB - shift));
+  r = km_dd_add(r, km_two_sum(scalbn(bh, 32 - shift), scalbn(bl, -shift)));
+  return r;
+}
+// one (cluster, dimension) term  c (2 S - n c)  on the grid 2^-(qg+QBg), as two limbs
+__device__ __forceinline__ void km_inertia_term(double c, long long Sa, long long Sb, long long cnt, int QB, int shift,
+                                                double scale_g, double scale_gb, long long &ga, long long &gb) {
+  ga = 0; gb = 0;
+  if (cnt <= 0) return;   // no members: S = 0, n = 0
+  KmDD S = km_fixed_to_dd(Sa, Sb, QB, shift);
+  S.hi = __dmul_rn(S.hi, 2.0); S.lo = __dmul_rn(S.lo, 2.0);
+  KmDD nc = km_two_prod((double)cnt, c);           // cnt < 2^53: exact as a double
+  nc.hi = -nc.hi; nc.lo = -nc.lo;
+  const KmDD g = km_dd_mul_d(km_dd_add(S, nc), c);
+  long long a, b;
+  km_fixed_split(g.hi, scale_g, scale_gb, a, b);
+  ga += a; gb += b;
+  km_fixed_split(g.lo, scale_g, scale_gb, a, b);
+  ga += a; gb += b;
+}
+// T (limbs on the grid 2^-(qt+QBt), set by max|x|) minus G (the sum of the terms above, limbs on the
+// grid 2^-(qg+QBg), set by max(max|x|, max|c|)) -> binary64.  Both limb pairs are exact as
+// double-doubles (<= 92 bits); the identity is >= 0 but its rounding may not be, hence the clamp.
+__device__ __forceinline__ double km_inertia_from_limbs(long long Ta, long long Tb, int QBt, int qt, long long Ga,
+                                                        long long Gb, int QBg, int qg) {
+  const KmDD T = km_fixed_to_dd(Ta, Tb, QBt, qt + QBt);
+  KmDD G = km_fixed_to_dd(Ga, Gb, QBg, qg + QBg);
+  G.hi = -G.hi; G.lo = -G.lo;
+  const KmDD r = km_dd_add(T, G);
+  const double v = __dadd_rn(r.hi, r.lo);
+  return v > 0.0 ? v : 0.0;
 }
 
 __device__ __forceinline__ long long km_warp_sum_ll(long long v) {

