@@ -96,8 +96,9 @@ static void free_points(km_ctx *ctx) {
   if (ctx->labels) cudaFree(ctx->labels);
   if (ctx->perm) cudaFree(ctx->perm);
   ctx->perm = nullptr; ctx->passes_since_upload = 0;
-  if (ctx->t_cand) cudaFree(ctx->t_cand);
-  ctx->t_cand = nullptr; ctx->t_cand_n = 0;
+  if (ctx->t_work) cudaFree(ctx->t_work);
+  if (ctx->t_order) cudaFree(ctx->t_order);
+  ctx->t_work = nullptr; ctx->t_order = nullptr; ctx->t_work_n = 0;
   ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
   ctx->n = 0; ctx->n_total = 0; ctx->i0 = 0;
 }
@@ -112,7 +113,8 @@ static void free_centroids(km_ctx *ctx) {
   for (int q = 0; q < 3; q++) { if (ctx->p1D[q]) cudaFree(ctx->p1D[q]); ctx->p1D[q] = nullptr; }
   if (ctx->t_cn) cudaFree(ctx->t_cn);
   if (ctx->t_cbf) cudaFree(ctx->t_cbf);
-  ctx->t_cn = nullptr; ctx->t_cbf = nullptr;
+  if (ctx->t_hist) cudaFree(ctx->t_hist);
+  ctx->t_cn = nullptr; ctx->t_cbf = nullptr; ctx->t_hist = nullptr; ctx->t_work_count = nullptr;
   ctx->p1 = false; ctx->p1_pending = false;
   ctx->have_centroids = false; ctx->k = 0; ctx->acc_len = 0;
 }
@@ -600,7 +602,7 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
   if (path == KM_PATH_FILTER_F32 && !km_small_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
     return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096, k*d <= 8192");
   if (path == KM_PATH_TENSOR && !km_tensor_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
-    return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR needs float32 points, d a multiple of 32 up to 128, k >= 2");
+    return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR needs float32 points, 9 <= d <= 128, k >= 2");
   const bool p1 = path == KM_PATH_FILTER_F32;
   if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len || ctx->p1 != p1 || ctx->path_now != path) {
     free_centroids(ctx);
@@ -622,8 +624,10 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
       if (ctx->world > 1) KM_CUDA(ctx, cudaMalloc(&ctx->acc_global, (size_t)L.len * sizeof(long long)));
       else ctx->acc_global = ctx->acc;
       if (path == KM_PATH_TENSOR) {
-        KM_CUDA(ctx, cudaMalloc(&ctx->t_cn, ((size_t)k + 512) * sizeof(float)));
+        KM_CUDA(ctx, cudaMalloc(&ctx->t_cn, km_tensor_h_bytes(k)));
         KM_CUDA(ctx, cudaMalloc(&ctx->t_cbf, km_tensor_cbf_bytes(d, k)));
+        KM_CUDA(ctx, cudaMalloc(&ctx->t_hist, ((size_t)k + 2) * sizeof(unsigned)));   // k + 1 buckets, then the worklist length
+        ctx->t_work_count = ctx->t_hist + (k + 1);
       }
     }
     ctx->k = k;
@@ -880,7 +884,8 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   }
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
-  a.t_cn = nullptr; a.t_cbf = nullptr; a.t_cand = nullptr; a.t_xnmax = 0.f;
+  a.t_cn = nullptr; a.t_cbf = nullptr; a.t_hist = nullptr; a.t_work_count = nullptr; a.t_order = nullptr; a.t_work = nullptr;
+  a.t_labels_fresh = 0; a.t_xnmax = 0.f;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
@@ -919,14 +924,20 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
   }
   const bool prof = ctx->cfg.profile_kernels != 0 && ctx->prof_n < KM_PROF_RING;
   if (prof) KM_CUDA(ctx, cudaEventRecord(ctx->prof_ev[ctx->prof_n][0], ctx->stream));
-  if (ctx->path_now == KM_PATH_TENSOR) {
-    if (ctx->t_cand_n < ctx->n) {
-      if (ctx->t_cand) cudaFree(ctx->t_cand);
-      ctx->t_cand = nullptr;
-      KM_CUDA(ctx, cudaMalloc(&ctx->t_cand, std::max<size_t>((size_t)ctx->n * KT_CAND * sizeof(int), 16)));
-      ctx->t_cand_n = ctx->n;
+  // beyond ~1e15 the binary32 scores of the coarse stage overflow: such a pass runs on the binary64 kernel
+  const double mag = sqrt((double)ctx->d) * std::max(ctx->maxabs, ctx->cbound);
+  if (ctx->path_now == KM_PATH_TENSOR && mag < 1e15) {
+    if (ctx->t_work_n < ctx->n || !ctx->t_work) {
+      if (ctx->t_work) cudaFree(ctx->t_work);
+      if (ctx->t_order) cudaFree(ctx->t_order);
+      ctx->t_work = nullptr; ctx->t_order = nullptr;
+      KM_CUDA(ctx, cudaMalloc(&ctx->t_work, km_tensor_work_bytes(ctx->n)));
+      KM_CUDA(ctx, cudaMalloc(&ctx->t_order, std::max<size_t>((size_t)ctx->n * sizeof(unsigned), 16)));
+      ctx->t_work_n = ctx->n;
     }
-    a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_cand = ctx->t_cand;
+    a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_hist = ctx->t_hist; a.t_work_count = ctx->t_work_count;
+    a.t_order = ctx->t_order; a.t_work = ctx->t_work;
+    a.t_labels_fresh = ctx->labels_fresh ? 1 : 0;
     a.t_xnmax = (float)(sqrt((double)ctx->d) * ctx->maxabs * (1.0 + 1e-6));
     KM_CUDA(ctx, km_launch_assign_tensor(a, &ctx->launches));
     ctx->last_path = KM_PATH_TENSOR;

@@ -10,7 +10,6 @@
 
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
-#define KT_CAND 8      // tensor path: survivors listed per point (two int4)
 #define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
 
 struct km_ctx {
@@ -87,10 +86,13 @@ struct km_ctx {
   int32_t p1_pend_it = 0;
 
   // ---- tensor path scratch
-  float *t_cn = nullptr;
-  void *t_cbf = nullptr;
-  int *t_cand = nullptr;
-  int64_t t_cand_n = 0;
+  float *t_cn = nullptr;            // -|chi_j|^2 / 2 per (padded) centroid
+  void *t_cbf = nullptr;            // BF16 copy of the centroids
+  unsigned *t_hist = nullptr;       // k + 1 bucket cursors of the label-ordered index list
+  unsigned *t_work_count = nullptr;
+  unsigned *t_order = nullptr;      // [n] point indices ordered by previous label
+  int *t_work = nullptr;            // [n] worklist entries of the exact stage
+  int64_t t_work_n = 0;
   int path_now = 0;                 // KM_PATH_* chosen for the current (points, centroids)
 
   // ---- multi-GPU
@@ -119,9 +121,11 @@ struct KmAssignArgs {
   float h_tau_hilo, h_tau_hi;
   int hilo;            // small-d filter: 1 = hi/lo binary32 centroid pairs (tighter bound, +1 op)
   KmPass ps;           // small-d path: the pass's sums / centroids / delta tables
-  float *t_cn;         // tensor path: |chi_j|^2 (padded)
-  void *t_cbf;         // tensor path: BF16 copy of the centroids, [kpad][dpad]
-  int *t_cand;         // tensor path: [n][KT_CAND] survivors of the coarse stage
+  float *t_cn;         // tensor path: -|chi_j|^2 / 2 (padded with -inf)
+  void *t_cbf;         // tensor path: BF16 copy of the centroids, [kpad][kblocks*64]
+  unsigned *t_hist, *t_work_count, *t_order;
+  int *t_work;         // tensor path: worklist of the exact stage
+  int t_labels_fresh;  // every label is still -1: no point ordering the points by it
   float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
   KmPrune2 pr;
@@ -135,6 +139,8 @@ cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches);
 cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches);
 bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 size_t km_tensor_cbf_bytes(int32_t d, int32_t k);
+size_t km_tensor_h_bytes(int32_t k);
+size_t km_tensor_work_bytes(int64_t n);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           KmPrune2 *out);
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);

@@ -1,11 +1,13 @@
-"""Small driver for ncu captures of the tensor path: python profiles/tensor_prof.py n d k iters"""
+"""Small driver for ncu captures of the tensor path: python profiles/tensor_prof.py n d k iters [k_true]"""
+import os
 import sys
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import kmeans_b200 as km
 n, d, k, iters = (int(v) for v in sys.argv[1:5])
+k_true = int(sys.argv[5]) if len(sys.argv) > 5 else k
 with km.KMeansState(path=km._lib.PATH_TENSOR) as st:
-    st.generate_blobs(n, d, k, 3)
-    st.init_forgy(k, 3)
+    st.generate_blobs(n, d, k_true, 4)
+    st.init_forgy(k, 4)
     for _ in range(iters):
         s = st.step()
-    print(s)
+        print(s)

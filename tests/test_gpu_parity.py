@@ -600,7 +600,8 @@ def test_pruned_attached_points_stay_unsorted(km):
 # ---------------------------------------------------------------- tensor path (tcgen05 coarse stage + exact stage)
 @pytest.mark.parametrize("mode", [0, 1], ids=["incremental", "full"])
 @pytest.mark.parametrize("shape", [(3000, 32, 16, 16), (1500, 128, 8, 32), (20000, 64, 40, 200), (4099, 32, 3, 129),
-                                   (9000, 96, 500, 1024), (257, 128, 2, 2)],
+                                   (9000, 96, 500, 1024), (257, 128, 2, 2), (6000, 16, 12, 40), (5003, 24, 9, 130),
+                                   (3001, 9, 5, 17), (2500, 77, 6, 300), (70000, 48, 64, 64)],
                          ids=lambda s: "n%d_d%d_kt%d_k%d" % s)
 def test_tensor_path_matches_oracle(km, shape, mode):
     n, d, k_true, k = shape
@@ -639,7 +640,7 @@ def test_tensor_path_near_ties_and_duplicates(km):
 
 
 def test_tensor_path_rejects_unsupported_shapes(km):
-    x = oracle.gen_blobs(1, 500, 48, 3)   # d not a multiple of 32
+    x = oracle.gen_blobs(1, 500, 200, 3)   # d beyond the 128 columns of one operand row
     with km.KMeansState(path=km._lib.PATH_TENSOR) as st:
         st.upload_points(x)
         with pytest.raises(km.KMeansError) as e:
