@@ -116,6 +116,12 @@ __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&v)[32
       : "r"(taddr)
       : "memory");
 }
+// 16-byte read-only load that does not allocate in L1 (data read exactly once)
+__device__ __forceinline__ float4 ldg_stream4(const float *p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 // max of three (FMNMX3)
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float r;
@@ -147,6 +153,7 @@ __device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
 static __host__ __device__ inline int kt_kblocks(int d) { return (d + 63) / 64; }
 static __host__ __device__ inline int kt_bstages(int d) { return kt_kblocks(d) == 1 ? 4 : 2; }
 static __host__ __device__ inline int kt_astages(int d) { return kt_kblocks(d) == 1 ? 4 : 2; }   // short rows: more passes in flight
+// plus, when it fits, a copy of h (one float per padded centroid) — see kt_h_in_smem
 static __host__ __device__ inline size_t kt_smem_bytes(int d) {
   return (size_t)(kt_astages(d) * 2 + kt_bstages(d)) * kt_kblocks(d) * KT_KB_BYTES   // A stages (two tiles each) + B stages
          + (size_t)KT_LIST * KT_ROWS * 8                                               // survivor lists
@@ -276,6 +283,7 @@ struct KtParams {
   const int32_t *labels;   // previous labels
   const __nv_bfloat16 *cbf;  // [kpad][kblocks*64] BF16 centroids (the TMA source; also read for the seed)
   const float *h;          // [kpad] -|chi_j|^2 / 2, -inf beyond k
+  int h_in_smem;           // the launcher found room for a shared-memory copy of h
   const KmState *st;       // st->cnmax2 = max_j |chi_j|^2
   float xnmax;             // upper bound of |x_i| over the job
   int *work;               // worklist entries, KT_WORK_INTS ints each
@@ -325,6 +333,11 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   uint64_t *a_full = bars, *a_empty = bars + 4, *b_full = bars + 8, *b_empty = bars + 12, *acc_full = bars + 16,
            *acc_empty = bars + 18;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
+  float *hs = reinterpret_cast<float *>(bars + 32);             // [kpad] copy of h when p.h_in_smem
+  const int kpad_h = ((p.k + KT_N - 1) / KT_N) * KT_N;
+  if (p.h_in_smem)
+    for (int j = threadIdx.x; j < kpad_h; j += KT_THREADS) hs[j] = p.h[j];
+  const float *hp = p.h_in_smem ? hs : p.h;   // generic pointer: shared or global (L1 is too small to keep h under the x stream)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // the operand region starts as zeros: the padding columns (d .. kblocks*64) are never written again
@@ -383,7 +396,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
           if (gi[u] >= 0) {
             const float *src = p.x + gi[u] * (int64_t)d + e;
             if (vec) {
-              v[u] = __ldg(reinterpret_cast<const float4 *>(src));
+              v[u] = ldg_stream4(src);          // read once: keep it out of L1
             } else {
               v[u].x = __ldg(src);
               if (e + 1 < d) v[u].y = __ldg(src + 1);
@@ -487,17 +500,24 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         const int rr = quad * 32 + lane;
         const unsigned char *arow = smem_raw + (size_t)(sa * 2 + m) * tile_bytes + rr * 128;
         const __nv_bfloat16 *crow = p.cbf + (int64_t)(seeded ? lab : 0) * drow;
-        for (int c8 = 0; c8 < nks * 2; c8++) {           // 16-byte pieces (8 values) up to d rounded to 16
-          const int kbi = c8 >> 3, chn = c8 & 7;
-          const uint4 xa = *reinterpret_cast<const uint4 *>(arow + kbi * KT_KB_BYTES + ((chn ^ (rr & 7)) << 4));
-          const uint4 cb = __ldg(reinterpret_cast<const uint4 *>(crow + c8 * 8));
-          const unsigned xw[4] = {xa.x, xa.y, xa.z, xa.w}, cw[4] = {cb.x, cb.y, cb.z, cb.w};
+        for (int kbi = 0; kbi < kblocks; kbi++) {        // one 64-value k-block at a time: its 8 loads fly together
+          uint4 cb[8];
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const float x0 = __uint_as_float(xw[u] << 16), x1 = __uint_as_float(xw[u] & 0xFFFF0000u);
-            const float c0 = __uint_as_float(cw[u] << 16), c1 = __uint_as_float(cw[u] & 0xFFFF0000u);
-            n2 = fmaf(x0, x0, n2); n2 = fmaf(x1, x1, n2);
-            dot = fmaf(x0, c0, dot); dot = fmaf(x1, c1, dot);
+          for (int chn = 0; chn < 8; chn++)
+            cb[chn] = (kbi * 8 + chn < nks * 2) ? __ldg(reinterpret_cast<const uint4 *>(crow + kbi * 64 + chn * 8)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int chn = 0; chn < 8; chn++) {
+            if (kbi * 8 + chn < nks * 2) {                // 16-byte pieces (8 values) up to d rounded to 16
+              const uint4 xa = *reinterpret_cast<const uint4 *>(arow + kbi * KT_KB_BYTES + ((chn ^ (rr & 7)) << 4));
+              const unsigned xw[4] = {xa.x, xa.y, xa.z, xa.w}, cw[4] = {cb[chn].x, cb[chn].y, cb[chn].z, cb[chn].w};
+#pragma unroll
+              for (int u = 0; u < 4; u++) {
+                const float x0 = __uint_as_float(xw[u] << 16), x1 = __uint_as_float(xw[u] & 0xFFFF0000u);
+                const float c0 = __uint_as_float(cw[u] << 16), c1 = __uint_as_float(cw[u] & 0xFFFF0000u);
+                n2 = fmaf(x0, x0, n2); n2 = fmaf(x1, x1, n2);
+                dot = fmaf(x0, c0, dot); dot = fmaf(x1, c1, dot);
+              }
+            }
           }
         }
         dot = seeded ? dot + __ldg(p.h + lab) : NEG_INF;
@@ -516,7 +536,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         float s[32];
 #pragma unroll
         for (int i4 = 0; i4 < 8; i4++) {
-          const float4 h4 = __ldg(reinterpret_cast<const float4 *>(p.h + col0) + i4);   // warp-uniform address
+          const float4 h4 = *(reinterpret_cast<const float4 *>(hp + col0) + i4);   // warp-uniform address
           s[i4 * 4 + 0] = __uint_as_float(v[i4 * 4 + 0]); s[i4 * 4 + 1] = __uint_as_float(v[i4 * 4 + 1]);
           s[i4 * 4 + 2] = __uint_as_float(v[i4 * 4 + 2]); s[i4 * 4 + 3] = __uint_as_float(v[i4 * 4 + 3]);
           add2(s[i4 * 4 + 0], s[i4 * 4 + 1], h4.x, h4.y);
@@ -814,7 +834,9 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   p.cbf = (const __nv_bfloat16 *)a.t_cbf;
   p.st = a.state; p.xnmax = a.t_xnmax; p.work = a.t_work; p.work_count = a.t_work_count;
   p.all_to_work = a.incremental ? 0 : 1;
-  const size_t smem = kt_smem_bytes(a.d);
+  size_t smem = kt_smem_bytes(a.d);
+  p.h_in_smem = smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
+  if (p.h_in_smem) smem += (size_t)kpad * sizeof(float);
   e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t passes = (a.n + KT_ROWS - 1) / KT_ROWS;
