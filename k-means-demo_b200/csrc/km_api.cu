@@ -98,7 +98,8 @@ static void free_points(km_ctx *ctx) {
   ctx->perm = nullptr; ctx->passes_since_upload = 0;
   if (ctx->t_work) cudaFree(ctx->t_work);
   if (ctx->t_order) cudaFree(ctx->t_order);
-  ctx->t_work = nullptr; ctx->t_order = nullptr; ctx->t_work_n = 0;
+  if (ctx->t_xn) cudaFree(ctx->t_xn);
+  ctx->t_work = nullptr; ctx->t_order = nullptr; ctx->t_xn = nullptr; ctx->t_work_n = 0; ctx->t_xn_valid = false;
   ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
   ctx->n = 0; ctx->n_total = 0; ctx->i0 = 0;
 }
@@ -376,6 +377,7 @@ static km_status alloc_points(km_ctx *ctx, int64_t n, int32_t d, int32_t dtype, 
   // step must not pay cudaMalloc/cudaFree)
   if (alloc_x && ctx->own_x && ctx->x && ctx->labels && ctx->n == n && ctx->d == d && ctx->dtype == dtype) {
     ctx->have_points = false;
+    ctx->t_xn_valid = false;              // new rows: their norms are not known yet
     if (ctx->perm) cudaFree(ctx->perm);   // new rows arrive in the caller's order
     ctx->perm = nullptr; ctx->passes_since_upload = 0;
     return KM_OK;
@@ -885,7 +887,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
   a.t_cn = nullptr; a.t_cbf = nullptr; a.t_hist = nullptr; a.t_work_count = nullptr; a.t_order = nullptr; a.t_work = nullptr;
-  a.t_labels_fresh = 0; a.t_xnmax = 0.f;
+  a.t_labels_fresh = 0; a.t_xnmax = 0.f; a.t_xn = nullptr;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
@@ -930,11 +932,19 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
     if (ctx->t_work_n < ctx->n || !ctx->t_work) {
       if (ctx->t_work) cudaFree(ctx->t_work);
       if (ctx->t_order) cudaFree(ctx->t_order);
-      ctx->t_work = nullptr; ctx->t_order = nullptr;
+      if (ctx->t_xn) cudaFree(ctx->t_xn);
+      ctx->t_work = nullptr; ctx->t_order = nullptr; ctx->t_xn = nullptr;
       KM_CUDA(ctx, cudaMalloc(&ctx->t_work, km_tensor_work_bytes(ctx->n)));
       KM_CUDA(ctx, cudaMalloc(&ctx->t_order, std::max<size_t>((size_t)ctx->n * sizeof(unsigned), 16)));
+      KM_CUDA(ctx, cudaMalloc(&ctx->t_xn, std::max<size_t>((size_t)ctx->n * sizeof(float), 16)));
       ctx->t_work_n = ctx->n;
+      ctx->t_xn_valid = false;
     }
+    if (!ctx->t_xn_valid) {   // once per upload
+      KM_CUDA(ctx, km_launch_row_norms((const float *)ctx->x, ctx->n, ctx->d, ctx->t_xn, ctx->sm_count, ctx->stream, &ctx->launches));
+      ctx->t_xn_valid = true;
+    }
+    a.t_xn = ctx->t_xn;
     a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_hist = ctx->t_hist; a.t_work_count = ctx->t_work_count;
     a.t_order = ctx->t_order; a.t_work = ctx->t_work;
     a.t_labels_fresh = ctx->labels_fresh ? 1 : 0;

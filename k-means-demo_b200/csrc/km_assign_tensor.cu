@@ -181,6 +181,31 @@ __global__ void __launch_bounds__(256) km_tensor_prep_kernel(const float *__rest
   }
 }
 
+// ------------------------------------------------------------------ |x_i| per point, once per upload
+// Eight lanes per row; the BF16 window of a point scales with its own norm instead of the job's largest.
+__global__ void __launch_bounds__(256) km_row_norm_kernel(const float *__restrict__ x, int64_t n, int d, float *__restrict__ xn) {
+  const int lane = threadIdx.x & 31, sl = lane & 7;
+  const int64_t grp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3, ngrp = ((int64_t)gridDim.x * blockDim.x) >> 3;
+  for (int64_t base = grp0 - (lane >> 3); base < n; base += ngrp) {   // base: first row of this warp's four
+    const int64_t i = base + (lane >> 3);
+    float s = 0.f;
+    if (i < n)
+      for (int t = sl; t < d; t += 8) { const float v = x[i * (int64_t)d + t]; s = fmaf(v, v, s); }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (i < n && sl == 0) xn[i] = sqrtf(s);
+  }
+}
+
+cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches) {
+  if (n == 0) return cudaSuccess;
+  const int64_t want = (n * 8 + 255) / 256, cap = (int64_t)sm_count * 16;
+  km_row_norm_kernel<<<(int)(want < cap ? want : cap), 256, 0, s>>>(x, n, d, xn);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ order: counting sort by previous label
 // Bucket k holds the never-assigned points (label < 0).  Any order inside a bucket will do.
 #define KO_THREADS 256
@@ -281,7 +306,7 @@ struct KtParams {
   int d, k;
   const unsigned *order;   // [n] row processed at position r, or nullptr = r itself
   const int32_t *labels;   // previous labels
-  const __nv_bfloat16 *cbf;  // [kpad][kblocks*64] BF16 centroids (the TMA source; also read for the seed)
+  const float *xn;         // [n] |x_i| (binary32, km_row_norm_kernel)
   const float *h;          // [kpad] -|chi_j|^2 / 2, -inf beyond k
   int h_in_smem;           // the launcher found room for a shared-memory copy of h
   const KmState *st;       // st->cnmax2 = max_j |chi_j|^2
@@ -345,8 +370,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     *reinterpret_cast<uint4 *>(smem_raw + o) = make_uint4(0, 0, 0, 0);
   fence_proxy_async();
   if (threadIdx.x == 0) {
-    // an operand stage is free again once its MMAs are done AND the epilogue warps have read their rows of it
-    for (int s = 0; s < 4; s++) { mbar_init(&a_full[s], KT_PROD_WARPS * 32); mbar_init(&a_empty[s], 1 + KT_EPI_WARPS); }
+    for (int s = 0; s < 4; s++) { mbar_init(&a_full[s], KT_PROD_WARPS * 32); mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < 4; s++) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
     for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], KT_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -358,6 +382,16 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   const uint32_t tmem_base = *tmem_slot;
   const int ntiles = (p.k + KT_N - 1) / KT_N;
   const int64_t passes = (p.n + KT_ROWS - 1) / KT_ROWS;
+
+  // The centroid tiles of a pass stream by starting with the tile that holds the previous label of the
+  // pass's first point (the index list is label-ordered: nearly all 256 points share it), so the running
+  // maximum is tight from the first chunk on.  Every role derives the same rotation from global memory.
+  auto pass_start = [&](int64_t ps) -> int {
+    const int64_t row0 = ps * KT_ROWS;
+    if (ps >= passes || row0 >= p.n) return 0;
+    const int lab = __ldg(p.labels + (p.order ? (int64_t)__ldg(p.order + row0) : row0));
+    return (lab >= 0 && lab < p.k) ? lab : 0;
+  };
 
   if (warp >= KT_EPI_WARPS && warp < KT_WARP_MMA) {
     // ===================== producers: rows of x -> BF16, K-major, swizzled =====================
@@ -426,14 +460,20 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     // ===================== TMA: centroid tiles =====================
     if (lane == 0) {
       uint32_t g = 0;
-      for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x)
+      int lab_next = pass_start(blockIdx.x);
+      for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
+        const int t0 = lab_next / KT_N;
+        lab_next = pass_start(ps + gridDim.x);      // fetched a pass ahead
         for (int t = 0; t < ntiles; t++, g++) {
           const uint32_t sb = g % bstages;
+          int tt = t0 + t;
+          if (tt >= ntiles) tt -= ntiles;
           mbar_wait(&b_empty[sb], ((g / bstages) & 1) ^ 1);
           mbar_expect_tx(&b_full[sb], tile_bytes);
           for (int kbi = 0; kbi < kblocks; kbi++)
-            tma_load_2d(sB + sb * tile_bytes + kbi * KT_KB_BYTES, &tmB, kbi * 64, t * KT_N, &b_full[sb]);
+            tma_load_2d(sB + sb * tile_bytes + kbi * KT_KB_BYTES, &tmB, kbi * 64, tt * KT_N, &b_full[sb]);
         }
+      }
     }
   } else if (warp == KT_WARP_MMA) {
     // ===================== MMA issue =====================
@@ -468,65 +508,34 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     // BF16 keeps 8 significant bits: unit roundoff u = 2^-8 per operand, a product errs by (2u + u^2)|x_t c_t|,
     // the score x~.c~ - |c|^2/2 by E/2 with E = (2^-6 + 2^-15) |x||c|.  Survivors: within
     // 2 * E/2 of the best score (plus slack for the fp32 accumulation and the rounding of h).
-    // Per point: |x| is its own norm (taken from the staged BF16 row, rounded up), |c| <= max_j |chi_j|.
+    // Per point: |x| is its own norm (computed once per upload, rounded up), |c| <= max_j |chi_j|.
     const float cnmax = sqrtf(p.st->cnmax2);
     const float NEG_INF = __int_as_float(0xff800000);
-    const int drow = kblocks * 64;
     uint32_t g = 0;
     int it = 0;
     // this point's row of x and its previous label, fetched one pass ahead
-    auto fetch_point = [&](int64_t ps, int &gi, int &lab) {
+    auto fetch_point = [&](int64_t ps, int &gi, int &lab, float &xnv) {
       const int64_t r = ps * KT_ROWS + row;
-      gi = -1; lab = -1;
+      gi = -1; lab = -1; xnv = 0.f;
       if (ps < passes && r < p.n) {
         gi = p.order ? (int)__ldg(p.order + r) : (int)r;
         lab = __ldg(p.labels + gi);
+        xnv = __ldg(p.xn + gi);
       }
     };
     int gi_next, lab_next;
-    fetch_point(blockIdx.x, gi_next, lab_next);
+    float xn_next;
+    fetch_point(blockIdx.x, gi_next, lab_next, xn_next);
+    int start_next = pass_start(blockIdx.x);
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
-      const int gi = gi_next, lab = lab_next;
+      const int gi = gi_next, lab = lab_next, start = start_next;
       const bool live = gi >= 0;
-      fetch_point(ps + gridDim.x, gi_next, lab_next);
-      // ---- seed of the running maximum: the BF16 score of the previous label, x~.c~ + h, from this thread's
-      // staged row and the BF16 centroid row — the very products the tensor core is about to form (up to
-      // the fp32 summation order, covered by the slack in `win`).  |x~|^2 comes out of the same loop.
-      const int sa = it % astages;
-      mbar_wait(&a_full[sa], (it / astages) & 1);
-      float dot = 0.f, n2 = 0.f;
-      {
-        const bool seeded = live && lab >= 0 && lab < p.k;
-        const int rr = quad * 32 + lane;
-        const unsigned char *arow = smem_raw + (size_t)(sa * 2 + m) * tile_bytes + rr * 128;
-        const __nv_bfloat16 *crow = p.cbf + (int64_t)(seeded ? lab : 0) * drow;
-        for (int kbi = 0; kbi < kblocks; kbi++) {        // one 64-value k-block at a time: its 8 loads fly together
-          uint4 cb[8];
-#pragma unroll
-          for (int chn = 0; chn < 8; chn++)
-            cb[chn] = (kbi * 8 + chn < nks * 2) ? __ldg(reinterpret_cast<const uint4 *>(crow + kbi * 64 + chn * 8)) : make_uint4(0, 0, 0, 0);
-#pragma unroll
-          for (int chn = 0; chn < 8; chn++) {
-            if (kbi * 8 + chn < nks * 2) {                // 16-byte pieces (8 values) up to d rounded to 16
-              const uint4 xa = *reinterpret_cast<const uint4 *>(arow + kbi * KT_KB_BYTES + ((chn ^ (rr & 7)) << 4));
-              const unsigned xw[4] = {xa.x, xa.y, xa.z, xa.w}, cw[4] = {cb[chn].x, cb[chn].y, cb[chn].z, cb[chn].w};
-#pragma unroll
-              for (int u = 0; u < 4; u++) {
-                const float x0 = __uint_as_float(xw[u] << 16), x1 = __uint_as_float(xw[u] & 0xFFFF0000u);
-                const float c0 = __uint_as_float(cw[u] << 16), c1 = __uint_as_float(cw[u] & 0xFFFF0000u);
-                n2 = fmaf(x0, x0, n2); n2 = fmaf(x1, x1, n2);
-                dot = fmaf(x0, c0, dot); dot = fmaf(x1, c1, dot);
-              }
-            }
-          }
-        }
-        dot = seeded ? dot + __ldg(p.h + lab) : NEG_INF;
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&a_empty[sa]);            // this warp is done with its rows of the stage
-      const float xn = fminf(sqrtf(n2) * 1.005f, p.xnmax);   // |x| <= |x~| (1 + 2^-8)
+      const float xn = fminf(xn_next * 1.0001f, p.xnmax);      // |x_i| (km_row_norm_kernel), rounded up
+      fetch_point(ps + gridDim.x, gi_next, lab_next, xn_next);
+      start_next = pass_start(ps + gridDim.x);
+      const int t0 = start / KT_N, c0 = (start % KT_N) >> 5;   // first tile, and the first chunk within it
       const float win = 0.0156556f * xn * cnmax + 1e-6f * (xn * xn + p.st->cnmax2);
-      float runmax = dot - 1e-6f * (xn * xn + p.st->cnmax2), thr = runmax - win;
+      float runmax = NEG_INF, thr = NEG_INF;
       int cnt = 0;
       float lostmax = NEG_INF;                // best score the full list had to let go
 
@@ -578,28 +587,32 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
 
       for (int t = 0; t < ntiles; t++, g++) {
         const uint32_t b = g & 1;
+        int tt = t0 + t;                          // the tile that arrives t-th (same rotation as the TMA thread's)
+        if (tt >= ntiles) tt -= ntiles;
+        // chunk order inside a tile: start where the previous label sits (it matters in the first tile only)
+        const int q0 = c0 * 32, q1 = ((c0 + 1) & 3) * 32, q2 = ((c0 + 2) & 3) * 32, q3 = ((c0 + 3) & 3) * 32;
         mbar_wait(&acc_full[b], (g >> 1) & 1);
         tc_fence_after();
         const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((m * 2 + b) * KT_N);
         uint32_t va[32], vb[32];
         __syncwarp();                             // tcgen05.ld / wait::ld are warp-collective: issue them converged
-        tmem_ld32_issue(tcol + 0, va);
+        tmem_ld32_issue(tcol + q0, va);
         tmem_ld_wait();
-        tmem_ld32_issue(tcol + 32, vb);           // the TMEM read of chunk c+1 is in flight while chunk c is processed
-        chunk(va, t * KT_N + 0);
+        tmem_ld32_issue(tcol + q1, vb);           // the TMEM read of chunk c+1 is in flight while chunk c is processed
+        chunk(va, tt * KT_N + q0);
         __syncwarp();
         tmem_ld_wait();
-        tmem_ld32_issue(tcol + 64, va);
-        chunk(vb, t * KT_N + 32);
+        tmem_ld32_issue(tcol + q2, va);
+        chunk(vb, tt * KT_N + q1);
         __syncwarp();
         tmem_ld_wait();
-        tmem_ld32_issue(tcol + 96, vb);
-        chunk(va, t * KT_N + 64);
+        tmem_ld32_issue(tcol + q3, vb);
+        chunk(va, tt * KT_N + q2);
         __syncwarp();
         tmem_ld_wait();
         tc_fence_before();
         if (lane == 0) mbar_arrive(&acc_empty[b]);   // this warp holds its last columns in registers: the buffer is free
-        chunk(vb, t * KT_N + 96);
+        chunk(vb, tt * KT_N + q3);
       }
 
       // ---- survivors of this point: within the window of the final maximum, ascending index
@@ -831,7 +844,7 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   if (e != cudaSuccess) return e;
   KtParams p;
   p.x = (const float *)a.x; p.n = a.n; p.d = a.d; p.k = a.k; p.order = order; p.labels = a.labels; p.h = a.t_cn;
-  p.cbf = (const __nv_bfloat16 *)a.t_cbf;
+  p.xn = a.t_xn;
   p.st = a.state; p.xnmax = a.t_xnmax; p.work = a.t_work; p.work_count = a.t_work_count;
   p.all_to_work = a.incremental ? 0 : 1;
   size_t smem = kt_smem_bytes(a.d);

@@ -92,6 +92,8 @@ struct km_ctx {
   unsigned *t_work_count = nullptr;
   unsigned *t_order = nullptr;      // [n] point indices ordered by previous label
   int *t_work = nullptr;            // [n] worklist entries of the exact stage
+  float *t_xn = nullptr;            // [n] |x_i|, computed on the first tensor pass after an upload
+  bool t_xn_valid = false;
   int64_t t_work_n = 0;
   int path_now = 0;                 // KM_PATH_* chosen for the current (points, centroids)
 
@@ -125,6 +127,7 @@ struct KmAssignArgs {
   void *t_cbf;         // tensor path: BF16 copy of the centroids, [kpad][kblocks*64]
   unsigned *t_hist, *t_work_count, *t_order;
   int *t_work;         // tensor path: worklist of the exact stage
+  const float *t_xn;   // tensor path: |x_i| per point
   int t_labels_fresh;  // every label is still -1: no point ordering the points by it
   float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
@@ -141,6 +144,7 @@ bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_opti
 size_t km_tensor_cbf_bytes(int32_t d, int32_t k);
 size_t km_tensor_h_bytes(int32_t k);
 size_t km_tensor_work_bytes(int64_t n);
+cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           KmPrune2 *out);
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
