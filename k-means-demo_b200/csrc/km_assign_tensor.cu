@@ -66,6 +66,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// the same for waiters that are usually early (producers, the TMA thread): sleep between polls so the
+// spin does not take issue slots from the epilogue warps of the same scheduler
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "WAIT_%=:\n\t"
+      "nanosleep.u32 64;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -121,6 +135,18 @@ __device__ __forceinline__ float4 ldg_stream4(const float *p) {
   float4 v;
   asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
+}
+// one lane of a converged warp (the compiler keeps single-thread tcgen05 / TMA issue cheap behind this predicate)
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred = 0, laneid = 0;
+  asm volatile(
+      "{\n\t.reg .b32 %%rx;\n\t.reg .pred %%px;\n\t"
+      "elect.sync %%rx|%%px, %2;\n\t"
+      "@%%px mov.s32 %1, 1;\n\t"
+      "mov.s32 %0, %%rx;\n\t}"
+      : "+r"(laneid), "+r"(pred)
+      : "r"(0xFFFFFFFFu));
+  return pred;
 }
 // max of three (FMNMX3)
 __device__ __forceinline__ float max3(float a, float b, float c) {
@@ -344,6 +370,9 @@ __device__ __noinline__ int kt_insert_full(int2 *lst, int row, float thr, int co
   return KT_LIST;
 }
 
+// HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
+// would wait in line behind the producers' stream of point loads)
+template <bool HSMEM>
 __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmB, const KtParams p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const int d = p.d, kblocks = kt_kblocks(d), bstages = kt_bstages(d);
@@ -360,9 +389,9 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
   float *hs = reinterpret_cast<float *>(bars + 32);             // [kpad] copy of h when p.h_in_smem
   const int kpad_h = ((p.k + KT_N - 1) / KT_N) * KT_N;
-  if (p.h_in_smem)
+  if (HSMEM)
     for (int j = threadIdx.x; j < kpad_h; j += KT_THREADS) hs[j] = p.h[j];
-  const float *hp = p.h_in_smem ? hs : p.h;   // generic pointer: shared or global (L1 is too small to keep h under the x stream)
+  const uint32_t hs_addr = smem_u32(hs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // the operand region starts as zeros: the padding columns (d .. kblocks*64) are never written again
@@ -418,7 +447,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     if ((int64_t)blockIdx.x < passes) fetch_idx((int64_t)blockIdx.x * KT_ROWS, pw * rpp + r_off, gi);
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
       const int s = it % astages;
-      mbar_wait(&a_empty[s], ((it / astages) & 1) ^ 1);
+      mbar_wait_relaxed(&a_empty[s], ((it / astages) & 1) ^ 1);
       const int64_t row0 = ps * KT_ROWS;
       unsigned char *stage = smem_raw + (size_t)s * 2 * tile_bytes;
       for (int rb0 = 0; rb0 < KT_ROWS; rb0 += BATCH * rstep) {
@@ -457,48 +486,58 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
       mbar_arrive(&a_full[s]);
     }
   } else if (warp == KT_WARP_TMA) {
-    // ===================== TMA: centroid tiles =====================
-    if (lane == 0) {
-      uint32_t g = 0;
-      int lab_next = pass_start(blockIdx.x);
-      for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
-        const int t0 = lab_next / KT_N;
-        lab_next = pass_start(ps + gridDim.x);      // fetched a pass ahead
-        for (int t = 0; t < ntiles; t++, g++) {
-          const uint32_t sb = g % bstages;
-          int tt = t0 + t;
-          if (tt >= ntiles) tt -= ntiles;
-          mbar_wait(&b_empty[sb], ((g / bstages) & 1) ^ 1);
+    // ===================== TMA: centroid tiles (the whole warp walks the loop, one elected lane issues) =====================
+    uint32_t g = 0;
+    int lab_next = pass_start(blockIdx.x);
+    for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
+      const int t0 = lab_next / KT_N;
+      lab_next = pass_start(ps + gridDim.x);      // fetched a pass ahead
+      for (int t = 0; t < ntiles; t++, g++) {
+        const uint32_t sb = g % bstages;
+        int tt = t0 + t;
+        if (tt >= ntiles) tt -= ntiles;
+        mbar_wait_relaxed(&b_empty[sb], ((g / bstages) & 1) ^ 1);
+        if (elect_one_sync()) {
           mbar_expect_tx(&b_full[sb], tile_bytes);
           for (int kbi = 0; kbi < kblocks; kbi++)
             tma_load_2d(sB + sb * tile_bytes + kbi * KT_KB_BYTES, &tmB, kbi * 64, tt * KT_N, &b_full[sb]);
         }
+        __syncwarp();
       }
     }
   } else if (warp == KT_WARP_MMA) {
-    // ===================== MMA issue =====================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(KT_M, KT_N);
-      uint32_t g = 0;
-      int it = 0;
-      for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
-        const int sa = it % astages;
-        mbar_wait(&a_full[sa], (it / astages) & 1);
-        for (int t = 0; t < ntiles; t++, g++) {
-          const uint32_t sb = g % bstages, b = g & 1;
-          mbar_wait(&b_full[sb], (g / bstages) & 1);
-          mbar_wait(&acc_empty[b], ((g >> 1) & 1) ^ 1);
-          tc_fence_after();
-          for (int m = 0; m < 2; m++)
-            for (int ks = 0; ks < nks; ks++) {
-              const uint32_t koff = (uint32_t)(ks >> 2) * KT_KB_BYTES + (uint32_t)(ks & 3) * 32;
-              umma_bf16(tmem_base + (uint32_t)((m * 2 + b) * KT_N), umma_desc_sw128(sA + (sa * 2 + m) * tile_bytes + koff),
-                        umma_desc_sw128(sB + sb * tile_bytes + koff), idesc, ks != 0);
+    // ===================== MMA issue (whole warp in the loop, one elected lane issues) =====================
+    const uint32_t idesc = umma_idesc_bf16(KT_M, KT_N);
+    uint32_t g = 0;
+    int it = 0;
+    for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
+      const int sa = it % astages;
+      mbar_wait_relaxed(&a_full[sa], (it / astages) & 1);
+      for (int t = 0; t < ntiles; t++, g++) {
+        const uint32_t sb = g % bstages, b = g & 1;
+        mbar_wait_relaxed(&b_full[sb], (g / bstages) & 1);
+        mbar_wait_relaxed(&acc_empty[b], ((g >> 1) & 1) ^ 1);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const uint64_t bdesc = umma_desc_sw128(sB + sb * tile_bytes);
+#pragma unroll
+          for (int m = 0; m < 2; m++) {
+            const uint64_t adesc = umma_desc_sw128(sA + (sa * 2 + m) * tile_bytes);
+            const uint32_t tacc = tmem_base + (uint32_t)((m * 2 + b) * KT_N);
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) {
+              if (ks < nks) {
+                // K step ks: k-block ks >> 2 (16 KiB apart), 32 bytes per step inside it; descriptor addresses are in 16-byte units
+                const uint64_t koff = (uint64_t)((ks >> 2) * (KT_KB_BYTES >> 4) + (ks & 3) * 2);
+                umma_bf16(tacc, adesc + koff, bdesc + koff, idesc, ks != 0);
+              }
             }
+          }
           umma_commit(&b_empty[sb]);          // the centroid tile may be overwritten once these MMAs are done
           umma_commit(&acc_full[b]);          // ... and the epilogue may read the accumulators
           if (t == ntiles - 1) umma_commit(&a_empty[sa]);
         }
+        __syncwarp();
       }
     }
   } else {
@@ -545,7 +584,12 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         float s[32];
 #pragma unroll
         for (int i4 = 0; i4 < 8; i4++) {
-          const float4 h4 = *(reinterpret_cast<const float4 *>(hp + col0) + i4);   // warp-uniform address
+          float4 h4;                                  // warp-uniform address: one broadcast
+          if (HSMEM)
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h4.x), "=f"(h4.y), "=f"(h4.z), "=f"(h4.w)
+                         : "r"(hs_addr + (uint32_t)(col0 + i4 * 4) * 4u));
+          else
+            h4 = __ldg(reinterpret_cast<const float4 *>(p.h + col0) + i4);
           s[i4 * 4 + 0] = __uint_as_float(v[i4 * 4 + 0]); s[i4 * 4 + 1] = __uint_as_float(v[i4 * 4 + 1]);
           s[i4 * 4 + 2] = __uint_as_float(v[i4 * 4 + 2]); s[i4 * 4 + 3] = __uint_as_float(v[i4 * 4 + 3]);
           add2(s[i4 * 4 + 0], s[i4 * 4 + 1], h4.x, h4.y);
@@ -850,10 +894,11 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   size_t smem = kt_smem_bytes(a.d);
   p.h_in_smem = smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
   if (p.h_in_smem) smem += (size_t)kpad * sizeof(float);
-  e = cudaFuncSetAttribute(km_tensor_coarse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  auto kern = p.h_in_smem ? km_tensor_coarse_kernel<true> : km_tensor_coarse_kernel<false>;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t passes = (a.n + KT_ROWS - 1) / KT_ROWS;
-  km_tensor_coarse_kernel<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmB, p);
+  kern<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmB, p);
   (*launches)++;
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
 
