@@ -266,6 +266,7 @@ static km_status reset_labels(km_ctx *ctx) {
   if (ctx->state) KM_CUDA(ctx, cudaMemsetAsync(&ctx->state->it, 0, sizeof(int32_t), ctx->stream));
   ctx->host_it = 0;
   ctx->labels_fresh = true;
+  ctx->t_order_valid = false;
   return KM_OK;
 }
 
@@ -887,7 +888,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
   a.t_cn = nullptr; a.t_cbf = nullptr; a.t_hist = nullptr; a.t_work_count = nullptr; a.t_order = nullptr; a.t_work = nullptr;
-  a.t_labels_fresh = 0; a.t_xnmax = 0.f; a.t_xn = nullptr;
+  a.t_labels_fresh = 0; a.t_order_reuse = 0; a.t_xnmax = 0.f; a.t_xn = nullptr;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
@@ -939,6 +940,7 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
       KM_CUDA(ctx, cudaMalloc(&ctx->t_xn, std::max<size_t>((size_t)ctx->n * sizeof(float), 16)));
       ctx->t_work_n = ctx->n;
       ctx->t_xn_valid = false;
+      ctx->t_order_valid = false;
     }
     if (!ctx->t_xn_valid) {   // once per upload
       KM_CUDA(ctx, km_launch_row_norms((const float *)ctx->x, ctx->n, ctx->d, ctx->t_xn, ctx->sm_count, ctx->stream, &ctx->launches));
@@ -948,6 +950,12 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
     a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_hist = ctx->t_hist; a.t_work_count = ctx->t_work_count;
     a.t_order = ctx->t_order; a.t_work = ctx->t_work;
     a.t_labels_fresh = ctx->labels_fresh ? 1 : 0;
+    // the first passes re-label many points: rebuild the list every time; later every fourth pass
+    a.t_order_reuse = (ctx->t_order_valid && ctx->host_it >= 6 && ctx->t_order_age < 3) ? 1 : 0;
+    if (!a.t_labels_fresh) {
+      if (a.t_order_reuse) ctx->t_order_age++;
+      else { ctx->t_order_valid = true; ctx->t_order_age = 0; }
+    }
     a.t_xnmax = (float)(sqrt((double)ctx->d) * ctx->maxabs * (1.0 + 1e-6));
     KM_CUDA(ctx, km_launch_assign_tensor(a, &ctx->launches));
     ctx->last_path = KM_PATH_TENSOR;

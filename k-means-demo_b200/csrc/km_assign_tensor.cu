@@ -415,10 +415,17 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   // The centroid tiles of a pass stream by starting with the tile that holds the previous label of the
   // pass's first point (the index list is label-ordered: nearly all 256 points share it), so the running
   // maximum is tight from the first chunk on.  Every role derives the same rotation from global memory.
-  auto pass_start = [&](int64_t ps) -> int {
-    const int64_t row0 = ps * KT_ROWS;
-    if (ps >= passes || row0 >= p.n) return 0;
-    const int lab = __ldg(p.labels + (p.order ? (int64_t)__ldg(p.order + row0) : row0));
+  // (Both look-ups are two dependent loads — index list, then label.  They are software-pipelined:
+  //  the index of pass p+2 and the label behind the index of pass p+1 are requested during pass p, so
+  //  neither latency is ever waited for.)
+  auto idx_at = [&](int64_t ps, int rowoff) -> int {          // level 1: which row of x sits at this position
+    const int64_t r = ps * KT_ROWS + rowoff;
+    if (ps >= passes || r >= p.n) return -1;
+    return p.order ? (int)__ldg(p.order + r) : (int)r;
+  };
+  auto start_of = [&](int gi0) -> int {                        // level 2: previous label of a pass's first point
+    if (gi0 < 0) return 0;
+    const int lab = __ldg(p.labels + gi0);
     return (lab >= 0 && lab < p.k) ? lab : 0;
   };
 
@@ -488,10 +495,12 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   } else if (warp == KT_WARP_TMA) {
     // ===================== TMA: centroid tiles (the whole warp walks the loop, one elected lane issues) =====================
     uint32_t g = 0;
-    int lab_next = pass_start(blockIdx.x);
+    int sg1 = idx_at((int64_t)blockIdx.x + gridDim.x, 0);
+    int start_next = start_of(idx_at(blockIdx.x, 0));
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
-      const int t0 = lab_next / KT_N;
-      lab_next = pass_start(ps + gridDim.x);      // fetched a pass ahead
+      const int t0 = start_next / KT_N;
+      start_next = start_of(sg1);                               // its index arrived a pass ago
+      sg1 = idx_at(ps + 2 * (int64_t)gridDim.x, 0);
       for (int t = 0; t < ntiles; t++, g++) {
         const uint32_t sb = g % bstages;
         int tt = t0 + t;
@@ -552,26 +561,26 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     const float NEG_INF = __int_as_float(0xff800000);
     uint32_t g = 0;
     int it = 0;
-    // this point's row of x and its previous label, fetched one pass ahead
-    auto fetch_point = [&](int64_t ps, int &gi, int &lab, float &xnv) {
-      const int64_t r = ps * KT_ROWS + row;
-      gi = -1; lab = -1; xnv = 0.f;
-      if (ps < passes && r < p.n) {
-        gi = p.order ? (int)__ldg(p.order + r) : (int)r;
-        lab = __ldg(p.labels + gi);
-        xnv = __ldg(p.xn + gi);
-      }
+    // this point's row of x (two passes ahead), its previous label and norm (one pass ahead)
+    auto point_of = [&](int gi_, int &lab_, float &xn_) {
+      lab_ = -1; xn_ = 0.f;
+      if (gi_ >= 0) { lab_ = __ldg(p.labels + gi_); xn_ = __ldg(p.xn + gi_); }
     };
-    int gi_next, lab_next;
+    int gi_next = idx_at(blockIdx.x, row), gi_n2 = idx_at((int64_t)blockIdx.x + gridDim.x, row);
+    int sg1 = idx_at((int64_t)blockIdx.x + gridDim.x, 0);
+    int lab_next;
     float xn_next;
-    fetch_point(blockIdx.x, gi_next, lab_next, xn_next);
-    int start_next = pass_start(blockIdx.x);
+    point_of(gi_next, lab_next, xn_next);
+    int start_next = start_of(idx_at(blockIdx.x, 0));
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
       const int gi = gi_next, lab = lab_next, start = start_next;
       const bool live = gi >= 0;
       const float xn = fminf(xn_next * 1.0001f, p.xnmax);      // |x_i| (km_row_norm_kernel), rounded up
-      fetch_point(ps + gridDim.x, gi_next, lab_next, xn_next);
-      start_next = pass_start(ps + gridDim.x);
+      gi_next = gi_n2;
+      point_of(gi_next, lab_next, xn_next);                     // their index arrived a pass ago
+      start_next = start_of(sg1);
+      gi_n2 = idx_at(ps + 2 * (int64_t)gridDim.x, row);
+      sg1 = idx_at(ps + 2 * (int64_t)gridDim.x, 0);
       const int t0 = start / KT_N, c0 = (start % KT_N) >> 5;   // first tile, and the first chunk within it
       const float win = 0.0156556f * xn * cnmax + 1e-6f * (xn * xn + p.st->cnmax2);
       float runmax = NEG_INF, thr = NEG_INF;
@@ -860,7 +869,9 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
 
   // ---- index list ordered by previous label (skipped while every label is still -1)
   const unsigned *order = nullptr;
-  if (a.t_order && !a.t_labels_fresh) {
+  if (a.t_order && !a.t_labels_fresh && a.t_order_reuse) {
+    order = a.t_order;   // a list from a few passes ago is still nearly label-ordered (and any order is correct)
+  } else if (a.t_order && !a.t_labels_fresh) {
     e = cudaMemsetAsync(a.t_hist, 0, ((size_t)a.k + 1) * sizeof(unsigned), a.stream);
     if (e != cudaSuccess) return e;
     const int blocks = (int)std::min<int64_t>((a.n + 16383) / 16384, (int64_t)a.sm_count * 8);

@@ -92,6 +92,8 @@ struct km_ctx {
   unsigned *t_work_count = nullptr;
   unsigned *t_order = nullptr;      // [n] point indices ordered by previous label
   int *t_work = nullptr;            // [n] worklist entries of the exact stage
+  bool t_order_valid = false;       // t_order holds a list built from this upload's labels
+  int t_order_age = 0;              // passes since it was built
   float *t_xn = nullptr;            // [n] |x_i|, computed on the first tensor pass after an upload
   bool t_xn_valid = false;
   int64_t t_work_n = 0;
@@ -129,6 +131,7 @@ struct KmAssignArgs {
   int *t_work;         // tensor path: worklist of the exact stage
   const float *t_xn;   // tensor path: |x_i| per point
   int t_labels_fresh;  // every label is still -1: no point ordering the points by it
+  int t_order_reuse;   // keep the index list of an earlier pass (rebuilt every few passes once the run has settled)
   float t_xnmax;       // tensor path: upper bound of |x_i|
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
   KmPrune2 pr;
