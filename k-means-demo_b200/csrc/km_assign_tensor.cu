@@ -177,6 +177,10 @@ __device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
 }
 
 static __host__ __device__ inline int kt_kblocks(int d) { return (d + 63) / 64; }
+// FOLD: when the padded row has 16 spare columns, -|c|^2/2 rides in the contraction itself: three extra
+// BF16 columns of the centroid copy hold h_j split into three 8-bit pieces (24 bits, as exact as the fp32 h),
+// the matching columns of every point row hold 1.0 — the accumulator IS the score, the epilogue adds nothing.
+static __host__ __device__ inline bool kt_fold(int d) { return ((d + 15) & ~15) + 16 <= kt_kblocks(d) * 64; }
 static __host__ __device__ inline int kt_bstages(int d) { return kt_kblocks(d) == 1 ? 4 : 2; }
 static __host__ __device__ inline int kt_astages(int d) { return kt_kblocks(d) == 1 ? 4 : 2; }   // short rows: more passes in flight
 // plus, when it fits, a copy of h (one float per padded centroid) — see kt_h_in_smem
@@ -191,7 +195,7 @@ static __host__ __device__ inline size_t kt_smem_bytes(int d) {
 // the BF16 copy of the row, zero beyond d and beyond k.
 __global__ void __launch_bounds__(256) km_tensor_prep_kernel(const float *__restrict__ chi, int k, int d, int kpad,
                                                              float *__restrict__ h, KmState *st,
-                                                             __nv_bfloat16 *__restrict__ cbf, int drow) {
+                                                             __nv_bfloat16 *__restrict__ cbf, int drow, int fold_col) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= kpad) return;
   float s = 0.f;
@@ -201,9 +205,21 @@ __global__ void __launch_bounds__(256) km_tensor_prep_kernel(const float *__rest
     cbf[(int64_t)warp * drow + t] = __float2bfloat16_rn((warp < k && t < d) ? chi[(int64_t)warp * d + t] : 0.f);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __syncwarp();   // the row's zero padding (written above by other lanes) precedes the three columns written below
   if (lane == 0) {
-    h[warp] = warp < k ? -0.5f * s : __int_as_float(0xff800000);
+    const float hv = -0.5f * s;
+    h[warp] = warp < k ? hv : __int_as_float(0xff800000);
     if (warp < k) atomicMax(reinterpret_cast<unsigned int *>(&st->cnmax2), __float_as_uint(s));   // s >= 0: bits order = value order
+    if (fold_col >= 0) {   // kt_fold: h as hi + mid + lo in three BF16 columns (a padding row scores -3e38, never +-inf)
+      const float hf = warp < k ? hv : -3.0e38f;
+      const __nv_bfloat16 b0 = __float2bfloat16_rn(hf);
+      const float r1 = warp < k ? hf - __bfloat162float(b0) : 0.f;
+      const __nv_bfloat16 b1 = __float2bfloat16_rn(r1);
+      const __nv_bfloat16 b2 = __float2bfloat16_rn(r1 - __bfloat162float(b1));
+      cbf[(int64_t)warp * drow + fold_col] = b0;
+      cbf[(int64_t)warp * drow + fold_col + 1] = b1;
+      cbf[(int64_t)warp * drow + fold_col + 2] = b2;
+    }
   }
 }
 
@@ -372,11 +388,11 @@ __device__ __noinline__ int kt_insert_full(int2 *lst, int row, float thr, int co
 
 // HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
 // would wait in line behind the producers' stream of point loads)
-template <bool HSMEM>
+template <bool HSMEM, bool FOLD>
 __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmB, const KtParams p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const int d = p.d, kblocks = kt_kblocks(d), bstages = kt_bstages(d);
-  const int nks = (d + 15) >> 4;                                // K = 16 MMA steps over the (zero-padded) dimension
+  const int nks = ((d + 15) >> 4) + (FOLD ? 1 : 0);             // K = 16 MMA steps over the (zero-padded) dimension [+ the h columns]
   const uint32_t tile_bytes = (uint32_t)kblocks * KT_KB_BYTES;   // one 128-row operand tile
   const int astages = kt_astages(d);
   const uint32_t sA = smem_u32(smem_raw);                        // [astages][2 tiles]
@@ -389,7 +405,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
   float *hs = reinterpret_cast<float *>(bars + 32);             // [kpad] copy of h when p.h_in_smem
   const int kpad_h = ((p.k + KT_N - 1) / KT_N) * KT_N;
-  if (HSMEM)
+  if (HSMEM && !FOLD)
     for (int j = threadIdx.x; j < kpad_h; j += KT_THREADS) hs[j] = p.h[j];
   const uint32_t hs_addr = smem_u32(hs);
 
@@ -397,6 +413,16 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   // the operand region starts as zeros: the padding columns (d .. kblocks*64) are never written again
   for (uint32_t o = threadIdx.x * 16; o < (uint32_t)astages * 2 * tile_bytes; o += KT_THREADS * 16)
     *reinterpret_cast<uint4 *>(smem_raw + o) = make_uint4(0, 0, 0, 0);
+  if (FOLD) {
+    // ... except the three columns that multiply the split h: 1.0 in every row of every stage
+    __syncthreads();
+    const int fc = ((d + 15) & ~15), fkb = fc >> 6, feb = fc & 63, fch = feb >> 3, fwithin = (feb & 7) * 2;
+    for (int r = threadIdx.x; r < astages * 2 * KT_M; r += KT_THREADS) {
+      const int rr = r & (KT_M - 1);
+      unsigned char *dst = smem_raw + (size_t)(r >> 7) * tile_bytes + fkb * KT_KB_BYTES + rr * 128 + ((fch ^ (rr & 7)) << 4) + fwithin;
+      *reinterpret_cast<uint2 *>(dst) = make_uint2(0x3F803F80u, 0x00003F80u);   // bf16 {1, 1, 1, 0}
+    }
+  }
   fence_proxy_async();
   if (threadIdx.x == 0) {
     for (int s = 0; s < 4; s++) { mbar_init(&a_full[s], KT_PROD_WARPS * 32); mbar_init(&a_empty[s], 1); }
@@ -591,8 +617,12 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
       // the window of its running maximum — a look at the columns one by one
       auto chunk = [&](uint32_t (&v)[32], int col0) {
         float s[32];
+        if (FOLD) {
 #pragma unroll
-        for (int i4 = 0; i4 < 8; i4++) {
+          for (int i = 0; i < 32; i++) s[i] = __uint_as_float(v[i]);   // the accumulator is the score
+        }
+#pragma unroll
+        for (int i4 = 0; i4 < (FOLD ? 0 : 8); i4++) {
           float4 h4;                                  // warp-uniform address: one broadcast
           if (HSMEM)
             asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(h4.x), "=f"(h4.y), "=f"(h4.z), "=f"(h4.w)
@@ -861,8 +891,9 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   const int drow = kt_kblocks(a.d) * 64;
   cudaError_t e = cudaMemsetAsync(&a.state->cnmax2, 0, sizeof(float), a.stream);
   if (e != cudaSuccess) return e;
+  const bool fold = kt_fold(a.d);
   km_tensor_prep_kernel<<<(kpad * 32 + 255) / 256, 256, 0, a.stream>>>(a.chi, a.k, a.d, kpad, a.t_cn, a.state,
-                                                                       (__nv_bfloat16 *)a.t_cbf, drow);
+                                                                       (__nv_bfloat16 *)a.t_cbf, drow, fold ? ((a.d + 15) & ~15) : -1);
   (*launches)++;
   if (a.n == 0) return cudaGetLastError();
   if (a.n >= ((int64_t)1 << 31)) return cudaErrorInvalidValue;   // worklist rows are 32-bit
@@ -903,9 +934,10 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   p.st = a.state; p.xnmax = a.t_xnmax; p.work = a.t_work; p.work_count = a.t_work_count;
   p.all_to_work = a.incremental ? 0 : 1;
   size_t smem = kt_smem_bytes(a.d);
-  p.h_in_smem = smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
+  p.h_in_smem = !fold && smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
   if (p.h_in_smem) smem += (size_t)kpad * sizeof(float);
-  auto kern = p.h_in_smem ? km_tensor_coarse_kernel<true> : km_tensor_coarse_kernel<false>;
+  auto kern = fold ? km_tensor_coarse_kernel<false, true>
+                   : (p.h_in_smem ? km_tensor_coarse_kernel<true, false> : km_tensor_coarse_kernel<false, false>);
   e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t passes = (a.n + KT_ROWS - 1) / KT_ROWS;
