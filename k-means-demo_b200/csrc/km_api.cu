@@ -476,6 +476,7 @@ extern "C" km_status km_destroy(km_ctx *ctx) {
   if (ctx->scan_bad) cudaFree(ctx->scan_bad);
   if (ctx->scan_bbox) cudaFree(ctx->scan_bbox);
   if (ctx->scan_t) cudaFree(ctx->scan_t);
+  if (ctx->cells_g) cudaFree(ctx->cells_g);
   for (int q = 0; q < KM_PROF_RING; q++)
     for (int w = 0; w < 2; w++) if (ctx->prof_ev[q][w]) cudaEventDestroy(ctx->prof_ev[q][w]);
   if (ctx->ring) cudaFreeHost(ctx->ring);
@@ -893,7 +894,8 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
     a.prune = 1;
-  a.sorted = (a.prune && ctx->perm && memcmp(&a.pr, &ctx->sort_pr, sizeof(KmPrune2)) == 0) ? 1 : 0;
+  a.sorted = (a.prune && ctx->perm && ctx->cells_g && memcmp(&a.pr, &ctx->sort_pr, sizeof(KmPrune2)) == 0) ? 1 : 0;
+  a.cells_g = ctx->cells_g;
 }
 
 // Store layout for the pruned d = 2 path: once a job has shown it iterates (third pass on the
@@ -910,6 +912,7 @@ static km_status maybe_sort_points(km_ctx *ctx) {
   KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
   ctx->x = x;
   ctx->sort_pr = pr;
+  if (!ctx->cells_g) KM_CUDA(ctx, cudaMalloc(&ctx->cells_g, (size_t)68 * 68 * sizeof(unsigned long long)));   // gp <= 68
   return KM_OK;
 }
 

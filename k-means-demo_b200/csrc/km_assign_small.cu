@@ -94,6 +94,7 @@ struct KmSmallParams {
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
   KmPrune2 pr;         // d == 2 candidate grid (used by the PRUNE instantiation)
   int sorted;          // PRUNE: the points are stored in ascending cell order of exactly this grid
+  const unsigned long long *cells_g;   // ... and the candidate words of this pass were built by km_prune_grid_kernel
 };
 
 // What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
@@ -195,6 +196,118 @@ __device__ __forceinline__ void km_load_labels(KmBatch<D> &b, const int32_t *__r
   }
 }
 
+// One warp builds the candidate word of one cell, lanes over the centroids (ncf: negated binary32
+// centroids, `crow` floats per row).  Same arithmetic, same words as the thread-per-cell build inside
+// the assignment kernel; the criterion is explained there.  The word is returned in every lane.
+__device__ __forceinline__ unsigned long long km_prune_cell_word(const float *ncf, int crow, int k, int cell,
+                                                                 const KmPrune2 &pr, float margin, int lane) {
+  const float hx = pr.inv_sx, hy = pr.inv_sy;
+  const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
+  const float mx = ((float)ix - pr.kx) * pr.inv_sx, my = ((float)iy - pr.ky) * pr.inv_sy;
+  unsigned long long bestkey = ~0ULL;   // (distance bits, index): min = nearest, lowest index on ties
+  for (int j = lane; j < k; j += 32) {
+    const float dx = mx + ncf[j * crow], dy = my + ncf[j * crow + 1];
+    const unsigned long long key = ((unsigned long long)__float_as_uint(fmaf(dx, dx, dy * dy)) << 32) | (unsigned)j;
+    bestkey = min(bestkey, key);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bestkey = min(bestkey, __shfl_xor_sync(0xffffffffu, bestkey, o));
+  const int bj = (int)(bestkey & 0xFFFFFFFFu);
+  const float dbest = __uint_as_float((unsigned)(bestkey >> 32));
+  const float bx = ncf[bj * crow], by = ncf[bj * crow + 1];
+  unsigned wlo = 0, whi = 0;
+  int cnt = 0;
+  for (int j0 = 0; j0 < k; j0 += 32) {
+    const int j = j0 + lane;
+    bool keep = false;
+    if (j < k) {
+      const float ncx = ncf[j * crow], ncy = ncf[j * crow + 1];
+      const float dx = mx + ncx, dy = my + ncy;
+      const float fm = fmaf(dx, dx, dy * dy) - dbest;
+      const float swing = fabsf(ncx - bx) * hx + fabsf(ncy - by) * hy;
+      keep = fm - swing <= margin;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      const int rank = cnt + __popc(bal & ((1u << lane) - 1u));
+      if (rank < KM_PRUNE_CAP) {
+        const unsigned long long w = (unsigned long long)j << (8 * (rank + 1));
+        wlo |= (unsigned)w;
+        whi |= (unsigned)(w >> 32);
+      }
+    }
+    cnt += __popc(bal);
+  }
+  wlo = __reduce_or_sync(0xffffffffu, wlo);
+  whi = __reduce_or_sync(0xffffffffu, whi);
+  return ((unsigned long long)whi << 32) | wlo | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
+}
+
+// the centroid coordinate the pass's prologue derives (same operations, same bits, wherever it is evaluated)
+__device__ __forceinline__ double km_small_centroid(const KmPass &ps, const KmAccLayout &L, int e, int D, bool pend, bool upd) {
+  const int jj = e / D;
+  long long sa = ps.S_in[L.sa + e], sb = ps.S_in[L.sb + e], cn = ps.S_in[L.cnt + jj];
+  if (pend) {
+    const long long da = ps.D_in[L.sa + e], db = ps.D_in[L.sb + e], dc = ps.D_in[L.cnt + jj];
+    if (ps.full_mode) { sa = da; sb = db; cn = dc; } else { sa += da; sb += db; cn += dc; }
+  }
+  double c = ps.C_in[e];
+  if (upd && cn > 0) c = __ddiv_rn(km_fixed_to_double(sa, sb, ps.QB, ps.qa + ps.QB), (double)cn);
+  return c;
+}
+
+// Cell-sorted d = 2 store: the candidate words of ALL cells, once per pass, by a small kernel in front of
+// the assignment kernel (16 cells per block, a warp per cell).  Each block first derives the pass's
+// centroids exactly as the assignment kernel's prologue will.  With the words in global memory no block
+// of the assignment kernel ever builds a grid or waits at a barrier for one.
+#define KM_GRID_THREADS 512
+__global__ void __launch_bounds__(KM_GRID_THREADS) km_prune_grid_kernel(const KmPass ps, int k, KmPrune2 pr, float cboundf,
+                                                                        unsigned long long *__restrict__ cells_g) {
+  extern __shared__ float gk_ncf[];   // [k][2] negated binary32 centroids
+  const KmAccLayout L = km_acc_layout(k, 2);
+  const bool pend = ps.D_in != nullptr;
+  const long long changed_prev = pend ? ps.D_in[L.scal + KM_ACC_CHANGED] : 0;
+  const bool upd = ps.apply_update && (!ps.needs_change || changed_prev > 0);
+  for (int e = threadIdx.x; e < k * 2; e += KM_GRID_THREADS)
+    gk_ncf[e] = -__double2float_rn(km_small_centroid(ps, L, e, 2, pend, upd));
+  __syncthreads();
+  const float prune_M = cboundf + pr.absmax;
+  const float margin = 1e-5f * prune_M * prune_M;
+  const int lane = threadIdx.x & 31;
+  const int cell = blockIdx.x * (KM_GRID_THREADS / 32) + (threadIdx.x >> 5);
+  if (cell < pr.gp * pr.gp) {
+    const unsigned long long w = km_prune_cell_word(gk_ncf, 2, k, cell, pr, margin, lane);
+    if (lane == 0) cells_g[cell] = w;
+  }
+}
+
+// The rare paths of the per-point tail live out of line: they would otherwise be replicated for every
+// point slot of a thread (the kernel's code outgrew the instruction cache) and hold registers hostage.
+template <int D>
+struct KmRow { float v[D]; };
+// binary64 argmin over all k in the oracle's operation order (A1/A2): strict <, lowest index wins
+template <int D>
+__device__ __noinline__ int km_small_rescore(KmRow<D> x, const double *cd, int k) {
+  double best = __longlong_as_double(0x7FF0000000000000LL);
+  int lab = 0;
+  for (int j = 0; j < k; j++) {
+    const double dj = km_dist2_f64(x.v, cd + (size_t)j * D, D);
+    if (dj < best) { best = dj; lab = j; }
+  }
+  return lab;
+}
+// one queued move (x, from, to) per lane into the block's table
+template <int D>
+__device__ __noinline__ void km_small_drain(long long *tab, int k, const unsigned *e, double scale_a, double scale_b) {
+  KmBlockTab T;
+  T.L = km_acc_layout(k, D);
+  T.tab = tab;
+  float xm[D];
+#pragma unroll
+  for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
+  km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
+}
+
 // Block 0, prologue: the inertia of the pending pass from the sums (km_common.cuh):
 // this warp's share of the terms c (2S - n c) over the merged sums and the centroids that pass
 // used (C_in), left in sg[warp][0..1].  Kept out of line so its double-double arithmetic costs
@@ -219,8 +332,9 @@ __device__ __noinline__ void km_small_inertia_terms(const long long *S_in, const
   if ((threadIdx.x & 31) == 0) { sg[threadIdx.x >> 5][0] = ga; sg[threadIdx.x >> 5][1] = gb; }
 }
 
-template <int D, bool HILO, bool PRUNE>
+template <int D, bool HILO, bool PRUNE, bool SORTED>
 __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
+  static_assert(!SORTED || PRUNE, "the cell-sorted store belongs to the pruned path");
   static_assert(!PRUNE || D == 2, "candidate pruning is built for d == 2");
   using Cfg = KmSmallCfg<D>;
   constexpr int PPV = Cfg::PPV, NV = Cfg::NV, PPT = Cfg::PPT, NP = Cfg::NP;
@@ -233,12 +347,16 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   double *cd = reinterpret_cast<double *>(ncf + (((size_t)k * CROW + 3) & ~(size_t)3));  // [k][D] binary64 masters
   long long *stab = reinterpret_cast<long long *>(cd + (size_t)k * D);               // optional per-block table
   const KmAccLayout L = km_acc_layout(k, D);
-  unsigned long long *cells =                                                         // PRUNE: candidate word per cell
-      reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal : 0));
+  // PRUNE: candidate word per cell — in shared memory, built by this block (points in the caller's order),
+  // or in global memory, built once per pass by km_prune_grid_kernel (cell-sorted store: a warp stays in
+  // one cell for thousands of points and reads its word through L1)
+  unsigned long long *cells_sm = reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal : 0));
+  constexpr bool cells_in_smem = PRUNE && !SORTED;
+  const unsigned long long *cells = cells_in_smem ? cells_sm : p.cells_g;
   // per-warp queue of points whose sums must move (x, from, to): filled by ballot, drained 32
   // at a time with every lane busy, instead of running the atomics under divergence
   constexpr int QCAP = 64, QW = D + 2;
-  unsigned *qbuf = reinterpret_cast<unsigned *>(cells + (PRUNE ? p.pr.gp * p.pr.gp : 0)) +
+  unsigned *qbuf = reinterpret_cast<unsigned *>(cells_sm + (cells_in_smem ? p.pr.gp * p.pr.gp : 0)) +
                    (threadIdx.x >> 5) * (QCAP * QW);
   int q_head = 0, q_count = 0;   // warp-uniform
   const KmPass &ps = p.ps;
@@ -247,20 +365,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   // inside the chunk is addressed with 32-bit offsets from the chunk's base
   constexpr int per_round = KM_SMALL_THREADS * PPT;
   auto chunk_len = [&](int64_t c) { return (int)max((int64_t)0, min(p.n - c * p.chunk, p.chunk)); };
-  // The two ends of a chunk of cell-sorted points give the cells it touches.  Thread 0 fetches
-  // them a chunk ahead straight into shared memory (asynchronous copy: nothing to keep in
-  // registers, nothing to wait for until the chunk starts).
-  __shared__ float2 s_ends[2];
-  auto fetch_chunk_ends = [&](int64_t c) {
-    const int len = chunk_len(c);
-    if (threadIdx.x == 0 && len > 0) {
-      const float2 *xc = reinterpret_cast<const float2 *>(p.x) + c * p.chunk;
-      km_cp_async8(&s_ends[0], xc);
-      km_cp_async8(&s_ends[1], xc + (len - 1));
-      km_cp_async_commit();
-    }
-  };
-
   // block 0 owes the host the pending pass's inertia: its terms first, while no register is live
   __shared__ long long s_g[KM_SMALL_THREADS / 32][2];   // per-warp shares of those terms
   if (blockIdx.x == 0 && ps.D_in != nullptr && ps.slot != nullptr)
@@ -268,10 +372,9 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
-  constexpr bool EARLY_LABELS = !PRUNE;   // see km_load_labels
+  constexpr bool EARLY_LABELS = true;     // labels travel with their points, a round ahead
   km_load_batch<D, EARLY_LABELS>(cur, p.x + (int64_t)blockIdx.x * p.chunk * D, p.labels + (int64_t)blockIdx.x * p.chunk, 0,
                                  chunk_len(blockIdx.x));
-  if (PRUNE && p.sorted) fetch_chunk_ends(blockIdx.x);
 
   // ---- prologue = the previous pass's centroid update (a4), redone by every block:
   //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
@@ -289,8 +392,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       const long long da = ps.D_in[L.sa + e], db = ps.D_in[L.sb + e], dc = ps.D_in[L.cnt + jj];
       if (ps.full_mode) { sa = da; sb = db; cn = dc; } else { sa += da; sb += db; cn += dc; }
     }
-    double c = ps.C_in[e];
-    if (upd && cn > 0) c = __ddiv_rn(km_fixed_to_double(sa, sb, ps.QB, ps.qa + ps.QB), (double)cn);
+    const double c = km_small_centroid(ps, L, e, D, pend, upd);
     const float h = __double2float_rn(c);
     ncf[jj * CROW + t] = -h;
     if (HILO) ncf[jj * CROW + D + t] = -__double2float_rn(__dsub_rn(c, (double)h));
@@ -335,7 +437,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const float rho2 = p.rho2;
   const unsigned mask = p.key_mask;
 
-  int cell_lo_b = 0, cell_hi_b = 0;   // PRUNE + sorted: the cell range built for the current chunk
   // Candidate list of a cell (a box with centre m and half sides hx/2, hy/2).  Let b be the
   // centroid nearest to m.  For any other centroid j,
   //     f_j(x) = |x - c_j|^2 - |x - c_b|^2 = a . x + const,   a = -2 (c_j - c_b)
@@ -376,59 +477,11 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           cnt++;
         }
       }
-      cells[cell] = word | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
-    }
-  };
-  // one warp per cell, lanes over the centroids: for the few cells one chunk of cell-sorted
-  // points touches.  Same arithmetic, same words as build_cells_all.
-  auto build_cells_range = [&](int lo, int hi) {
-    const KmPrune2 &pr = p.pr;
-    const float hx = pr.inv_sx, hy = pr.inv_sy;
-    for (int cell = lo + (int)(threadIdx.x >> 5); cell <= hi; cell += KM_SMALL_THREADS / 32) {
-      const int iy = cell / pr.gp, ix = cell - iy * pr.gp;
-      const float mx = ((float)ix - pr.kx) * pr.inv_sx, my = ((float)iy - pr.ky) * pr.inv_sy;
-      unsigned long long bestkey = ~0ULL;   // (distance bits, index): min = nearest, lowest index on ties
-      for (int j = lane; j < k; j += 32) {
-        const float dx = mx + ncf[j * CROW], dy = my + ncf[j * CROW + 1];
-        const unsigned long long key = ((unsigned long long)__float_as_uint(fmaf(dx, dx, dy * dy)) << 32) | (unsigned)j;
-        bestkey = min(bestkey, key);
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) bestkey = min(bestkey, __shfl_xor_sync(0xffffffffu, bestkey, o));
-      const int bj = (int)(bestkey & 0xFFFFFFFFu);
-      const float dbest = __uint_as_float((unsigned)(bestkey >> 32));
-      const float bx = ncf[bj * CROW], by = ncf[bj * CROW + 1];
-      unsigned wlo = 0, whi = 0;
-      int cnt = 0;
-      for (int j0 = 0; j0 < k; j0 += 32) {
-        const int j = j0 + lane;
-        bool keep = false;
-        if (j < k) {
-          const float ncx = ncf[j * CROW], ncy = ncf[j * CROW + 1];
-          const float dx = mx + ncx, dy = my + ncy;
-          const float fm = fmaf(dx, dx, dy * dy) - dbest;
-          const float swing = fabsf(ncx - bx) * hx + fabsf(ncy - by) * hy;
-          keep = fm - swing <= margin;
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-          const int rank = cnt + __popc(bal & ((1u << lane) - 1u));
-          if (rank < KM_PRUNE_CAP) {
-            const unsigned long long w = (unsigned long long)j << (8 * (rank + 1));
-            wlo |= (unsigned)w;
-            whi |= (unsigned)(w >> 32);
-          }
-        }
-        cnt += __popc(bal);
-      }
-      wlo = __reduce_or_sync(0xffffffffu, wlo);
-      whi = __reduce_or_sync(0xffffffffu, whi);
-      if (lane == 0)
-        cells[cell] = ((unsigned long long)whi << 32) | wlo | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
+      cells_sm[cell] = word | (unsigned long long)(cnt > KM_PRUNE_CAP ? 0xFF : cnt);
     }
   };
   if constexpr (PRUNE) {
-    if (!p.sorted) {
+    if (!SORTED) {
       build_cells_all();
       __syncthreads();
     }
@@ -441,17 +494,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const float *__restrict__ xb = p.x + ch * p.chunk * D;
   int32_t *__restrict__ lb = p.labels + ch * p.chunk;
   const int64_t ch_next = ch + gridDim.x;
-  if constexpr (PRUNE) {
-    if (p.sorted) {
-      // candidate words for the cells between this chunk's first and last point
-      if (threadIdx.x == 0) km_cp_async_wait_all();
-      __syncthreads();   // the chunk's ends have landed; the previous chunk's readers are done
-      cell_lo_b = cell_of(s_ends[0]);
-      cell_hi_b = max(cell_of(s_ends[1]), cell_lo_b);
-      build_cells_range(cell_lo_b, cell_hi_b);
-      __syncthreads();
-    }
-  }
   for (int r0 = 0; r0 < cn; r0 += per_round) {
     // software pipeline: the next round's loads (the next chunk's first, at the end of this
     // one) are in flight during this round's arithmetic
@@ -461,7 +503,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
       km_load_batch<D, EARLY_LABELS>(nxt, xb, lb, r0 + per_round, cn);
     } else if (ch_next < p.nchunks) {
       km_load_batch<D, EARLY_LABELS>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
-      if (PRUNE && p.sorted) fetch_chunk_ends(ch_next);
     }
 
     // ---- binary32 filter, top-2 on integer keys
@@ -481,16 +522,14 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
         // the end of a ragged round (a negative index shows up as a huge masked value)
         const int ix = min(__float_as_int(fmaf(x0, pr.sx, pr.kxm)) & 0x3FFFFF, pr.gp - 1);
         const int iy = min(__float_as_int(fmaf(x1, pr.sy, pr.kym)) & 0x3FFFFF, pr.gp - 1);
-        int cell = iy * pr.gp + ix;
-        if (p.sorted) cell = min(max(cell, cell_lo_b), cell_hi_b);   // dead lanes only: stay inside what was built
-        return cell;
+        return iy * pr.gp + ix;
       };
       // Do all 32 x PPT points of the warp share one candidate word?  With the points stored in
       // cell order nearly every warp does: the candidates are then warp-uniform (one broadcast
       // LDS each, no predication), and a single-candidate word needs no filter at all.
       unsigned long long w[PPT], w0 = 0;
       bool uniform = false;
-      if (p.sorted && r0 + per_round <= cn) {
+      if (SORTED && r0 + per_round <= cn) {
         // cell ids ascend along the store and every slot of a whole round is a real point: if
         // the warp's first and last point share a cell, so does everything between them
         const int ca = __shfl_sync(0xffffffffu, cell_of_q(0), 0);
@@ -648,12 +687,10 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           const bool clear = (m2[q] == 0xFFFFFFFFu) ? (m1[q] != 0xFFFFFFFFu) : ((b2 - b1) > fmaf(rho2, b2, tau2));
           if (live && !clear) {
             rescored++;
-            double best = __longlong_as_double(0x7FF0000000000000LL);
-            lab = 0;
-            for (int j = 0; j < k; j++) {
-              const double dj = km_dist2_f64(xr, cd + (size_t)j * D, D);
-              if (dj < best) { best = dj; lab = j; }
-            }
+            KmRow<D> row;
+#pragma unroll
+            for (int t = 0; t < D; t++) row.v[t] = xr[t];
+            lab = km_small_rescore<D>(row, cd, k);
           }
           if (!live) lab = cur.old[q];
           newlab[q] = lab;
@@ -687,11 +724,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           q_count += __popc(bal);
           __syncwarp();
           if (q_count >= 32) {
-            const unsigned *e = qbuf + ((q_head + lane) & (QCAP - 1)) * QW;
-            float xm[D];
-#pragma unroll
-            for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
-            km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
+            km_small_drain<D>(T.tab, k, qbuf + ((q_head + lane) & (QCAP - 1)) * QW, scale_a, scale_b);
             q_head = (q_head + 32) & (QCAP - 1);
             q_count -= 32;
             __syncwarp();
@@ -727,13 +760,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   }
 
   // whatever is still queued (fewer than 32 entries per warp)
-  if (lane < q_count) {
-    const unsigned *e = qbuf + ((q_head + lane) & (QCAP - 1)) * QW;
-    float xm[D];
-#pragma unroll
-    for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
-    km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
-  }
+  if (lane < q_count) km_small_drain<D>(T.tab, k, qbuf + ((q_head + lane) & (QCAP - 1)) * QW, scale_a, scale_b);
 
   // ---- block epilogue.  Counts go through one REDUX per warp.
   {
@@ -760,7 +787,7 @@ bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin
   return small_centroid_smem(d, k, true) + 4096 <= (size_t)max_smem_optin / 2;
 }
 
-template <int D, bool HILO, bool PRUNE>
+template <int D, bool HILO, bool PRUNE, bool SORTED>
 static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   const KmAccLayout L = km_acc_layout(a.k, D);
   size_t smem = small_centroid_smem(D, a.k, HILO);
@@ -780,13 +807,15 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   // (D+6) u for the arithmetic, 2^-(23-bits) for the key truncation, x2.5 margin
   p.rho2 = 2.5f * ((float)(D + 6) * 0x1.0p-24f + ldexpf(1.0f, bits - 23));
   p.sorted = 0;
+  p.cells_g = nullptr;
   if (PRUNE) {
     p.pr = a.pr;
-    p.sorted = a.sorted;
-    smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);
+    p.sorted = SORTED ? 1 : 0;
+    p.cells_g = a.cells_g;
+    if (!p.sorted) smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);   // the block builds its own copy
   }
   smem += (size_t)(KM_SMALL_THREADS / 32) * 64 * (D + 2) * sizeof(unsigned);   // per-warp move queues
-  auto kern = km_assign_small_kernel<D, HILO, PRUNE>;
+  auto kern = km_assign_small_kernel<D, HILO, PRUNE, SORTED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -823,6 +852,13 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   p.scale_b = a.scale_b;
   p.tau2 = HILO ? a.h_tau_hilo : a.h_tau_hi;
   p.cboundf = (float)a.h_cbound * 1.0000002f;
+  if (PRUNE && p.sorted && a.n > 0) {
+    // this pass's candidate words, for every cell, in front of the assignment kernel
+    const int cellsn = a.pr.gp * a.pr.gp;
+    km_prune_grid_kernel<<<(cellsn + KM_GRID_THREADS / 32 - 1) / (KM_GRID_THREADS / 32), KM_GRID_THREADS,
+                           (size_t)a.k * 2 * sizeof(float), a.stream>>>(a.ps, a.k, a.pr, p.cboundf, a.cells_g);
+    (*launches)++;
+  }
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
   (*launches)++;
   return cudaGetLastError();
@@ -831,14 +867,16 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
 template <bool HILO>
 static cudaError_t dispatch_small(const KmAssignArgs &a, int64_t *launches) {
   switch (a.d) {
-    case 1: return launch_small<1, HILO, false>(a, launches);
-    case 2: return a.prune ? launch_small<2, HILO, true>(a, launches) : launch_small<2, HILO, false>(a, launches);
-    case 3: return launch_small<3, HILO, false>(a, launches);
-    case 4: return launch_small<4, HILO, false>(a, launches);
-    case 5: return launch_small<5, HILO, false>(a, launches);
-    case 6: return launch_small<6, HILO, false>(a, launches);
-    case 7: return launch_small<7, HILO, false>(a, launches);
-    case 8: return launch_small<8, HILO, false>(a, launches);
+    case 1: return launch_small<1, HILO, false, false>(a, launches);
+    case 2:
+      if (!a.prune) return launch_small<2, HILO, false, false>(a, launches);
+      return (a.sorted && a.cells_g) ? launch_small<2, HILO, true, true>(a, launches) : launch_small<2, HILO, true, false>(a, launches);
+    case 3: return launch_small<3, HILO, false, false>(a, launches);
+    case 4: return launch_small<4, HILO, false, false>(a, launches);
+    case 5: return launch_small<5, HILO, false, false>(a, launches);
+    case 6: return launch_small<6, HILO, false, false>(a, launches);
+    case 7: return launch_small<7, HILO, false, false>(a, launches);
+    case 8: return launch_small<8, HILO, false, false>(a, launches);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -35,6 +35,7 @@ struct km_ctx {
   bool have_points = false;
   int32_t *labels = nullptr;  // device, n
   unsigned *perm = nullptr;   // device, n: original row of each stored row once the store was cell-sorted (km_sort.cu)
+  unsigned long long *cells_g = nullptr;   // device: candidate word per grid cell of the sorted store (rebuilt every pass)
   KmPrune2 sort_pr;           // the grid the stored order follows
   int passes_since_upload = 0;
   void *pinned = nullptr;     // staging for uploads / downloads
@@ -136,6 +137,7 @@ struct KmAssignArgs {
   int prune;           // small-d path, d == 2: use the candidate grid `pr`
   KmPrune2 pr;
   int sorted;          // ... and the points are stored in ascending cell order of `pr`
+  unsigned long long *cells_g;   // ... with room for one candidate word per cell (km_prune_grid_kernel)
   cudaStream_t stream;
 };
 
