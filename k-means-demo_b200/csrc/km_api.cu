@@ -892,10 +892,11 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.t_labels_fresh = 0; a.t_order_reuse = 0; a.t_xnmax = 0.f; a.t_xn = nullptr;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
-      km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &a.pr))
+      km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, ctx->perm ? 1 : 0, &a.pr))
     a.prune = 1;
   a.sorted = (a.prune && ctx->perm && ctx->cells_g && memcmp(&a.pr, &ctx->sort_pr, sizeof(KmPrune2)) == 0) ? 1 : 0;
   a.cells_g = ctx->cells_g;
+  a.work_counter = ctx->cells_g ? reinterpret_cast<unsigned *>(ctx->cells_g + (size_t)KM_PRUNE_MAX_GP * KM_PRUNE_MAX_GP) : nullptr;
 }
 
 // Store layout for the pruned d = 2 path: once a job has shown it iterates (third pass on the
@@ -907,12 +908,12 @@ static km_status maybe_sort_points(km_ctx *ctx) {
     return KM_OK;
   KmPrune2 pr;
   memset(&pr, 0, sizeof(pr));
-  if (!km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, &pr)) return KM_OK;
+  if (!km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, 1, &pr)) return KM_OK;
   float *x = (float *)ctx->x;
   KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
   ctx->x = x;
   ctx->sort_pr = pr;
-  if (!ctx->cells_g) KM_CUDA(ctx, cudaMalloc(&ctx->cells_g, (size_t)68 * 68 * sizeof(unsigned long long)));   // gp <= 68
+  if (!ctx->cells_g) KM_CUDA(ctx, cudaMalloc(&ctx->cells_g, ((size_t)KM_PRUNE_MAX_GP * KM_PRUNE_MAX_GP + 1) * sizeof(unsigned long long)));   // words + the work counter
   return KM_OK;
 }
 

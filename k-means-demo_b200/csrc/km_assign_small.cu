@@ -73,6 +73,16 @@ struct KmSmallCfg {
   static constexpr bool TAIL = (D & 1) != 0;                    // odd last dimension handled as a scalar
 };
 
+// Offset, within a round, of the first point of this thread's v-th vector.  A warp's NV vectors sit next to
+// each other, so the points of one warp-round are ONE contiguous range of 32 * PPT points (on the
+// cell-sorted store: usually a single cell).
+// WQ: rounds are per warp (32 * PPT points, handed out warp by warp), not per block.
+template <int NV, int PPV, bool WQ>
+__device__ __forceinline__ int km_slot(int v) {
+  return WQ ? (v * 32 + ((int)threadIdx.x & 31)) * PPV
+            : ((((int)threadIdx.x >> 5) * NV + v) * 32 + ((int)threadIdx.x & 31)) * PPV;
+}
+
 #define KM_PRUNE_MAGIC 12582912.0f
 #define KM_PRUNE_CAP 7   // candidates kept per cell (one 64-bit word: count byte + 7 indices)
 
@@ -95,6 +105,7 @@ struct KmSmallParams {
   KmPrune2 pr;         // d == 2 candidate grid (used by the PRUNE instantiation)
   int sorted;          // PRUNE: the points are stored in ascending cell order of exactly this grid
   const unsigned long long *cells_g;   // ... and the candidate words of this pass were built by km_prune_grid_kernel
+  unsigned *work_counter;              // ... and the next unit of work is taken from here
 };
 
 // What one thread holds for one round: PPT points as packed dimension pairs (+ the odd last
@@ -110,7 +121,7 @@ struct KmBatch {
 // Load the thread's NV vectors of round `r0` (first point index of the round) within the
 // block's chunk [.., c1).  A vector wholly inside the chunk is one 16-byte load (d = 1, 2, 4)
 // or a few 8/16-byte loads (other even d); the ragged end is read point by point.
-template <int D, bool LABELS = true>
+template <int D, bool LABELS = true, bool WQ = false>
 __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__restrict__ xb,
                                               const int32_t *__restrict__ lb, int r, int cn) {
   using Cfg = KmSmallCfg<D>;
@@ -118,7 +129,7 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
   constexpr bool TAIL = Cfg::TAIL;
 #pragma unroll
   for (int v = 0; v < NV; v++) {
-    const int i0 = r + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;   // offset within the chunk
+    const int i0 = r + km_slot<NV, PPV, WQ>(v);   // offset within the chunk
     if (i0 + PPV <= cn) {
       const float *row = xb + i0 * D;
       if constexpr (D == 1) {
@@ -172,13 +183,13 @@ __device__ __forceinline__ void km_load_batch(KmBatch<D> &b, const float *__rest
 // kernel fetches them at the top of the round they are used in rather than a round ahead: they
 // are not needed before the tail, and four fewer live registers keep the prefetched labels from
 // being spilled (a spill store waits for the load it spills — the prefetch would be lost).
-template <int D>
+template <int D, bool WQ = false>
 __device__ __forceinline__ void km_load_labels(KmBatch<D> &b, const int32_t *__restrict__ lb, int r, int cn) {
   using Cfg = KmSmallCfg<D>;
   constexpr int PPV = Cfg::PPV, NV = Cfg::NV;
 #pragma unroll
   for (int v = 0; v < NV; v++) {
-    const int i0 = r + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;
+    const int i0 = r + km_slot<NV, PPV, WQ>(v);
     if (i0 + PPV <= cn) {
       if constexpr (PPV == 4) {
         const int4 o = *reinterpret_cast<const int4 *>(lb + i0);
@@ -262,7 +273,7 @@ __device__ __forceinline__ double km_small_centroid(const KmPass &ps, const KmAc
 // of the assignment kernel ever builds a grid or waits at a barrier for one.
 #define KM_GRID_THREADS 512
 __global__ void __launch_bounds__(KM_GRID_THREADS) km_prune_grid_kernel(const KmPass ps, int k, KmPrune2 pr, float cboundf,
-                                                                        unsigned long long *__restrict__ cells_g) {
+                                                                        unsigned long long *__restrict__ cells_g, unsigned *work_counter) {
   extern __shared__ float gk_ncf[];   // [k][2] negated binary32 centroids
   const KmAccLayout L = km_acc_layout(k, 2);
   const bool pend = ps.D_in != nullptr;
@@ -279,6 +290,7 @@ __global__ void __launch_bounds__(KM_GRID_THREADS) km_prune_grid_kernel(const Km
     const unsigned long long w = km_prune_cell_word(gk_ncf, 2, k, cell, pr, margin, lane);
     if (lane == 0) cells_g[cell] = w;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *work_counter = 0;   // the assignment kernel's warps start counting here
 }
 
 // The rare paths of the per-point tail live out of line: they would otherwise be replicated for every
@@ -363,7 +375,19 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 
   // this block's contiguous chunk of points, walked in rounds of THREADS*PPT; everything
   // inside the chunk is addressed with 32-bit offsets from the chunk's base
-  constexpr int per_round = KM_SMALL_THREADS * PPT;
+  // Cell-sorted store: work per point depends on where it lies (how many candidates its cell has), so equal
+  // static shares are not equal work.  There the shard is cut into units of a few rounds which the WARPS
+  // of the grid take one after another from a global counter (zeroed by km_prune_grid_kernel).
+  constexpr bool WQ = SORTED;
+  constexpr int per_round = (WQ ? 32 : KM_SMALL_THREADS) * PPT;
+  const int lane = threadIdx.x & 31;
+  auto grab = [&]() -> int64_t {
+    unsigned u = 0;
+    if (lane == 0) u = atomicAdd(p.work_counter, 1u);
+    return (int64_t)__shfl_sync(0xffffffffu, u, 0);
+  };
+  int64_t ch = blockIdx.x, ch_next = (int64_t)blockIdx.x + gridDim.x;
+  if (WQ) { ch = grab(); ch_next = grab(); }
   auto chunk_len = [&](int64_t c) { return (int)max((int64_t)0, min(p.n - c * p.chunk, p.chunk)); };
   // block 0 owes the host the pending pass's inertia: its terms first, while no register is live
   __shared__ long long s_g[KM_SMALL_THREADS / 32][2];   // per-warp shares of those terms
@@ -373,8 +397,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
   constexpr bool EARLY_LABELS = true;     // labels travel with their points, a round ahead
-  km_load_batch<D, EARLY_LABELS>(cur, p.x + (int64_t)blockIdx.x * p.chunk * D, p.labels + (int64_t)blockIdx.x * p.chunk, 0,
-                                 chunk_len(blockIdx.x));
+  km_load_batch<D, EARLY_LABELS, WQ>(cur, p.x + ch * p.chunk * D, p.labels + ch * p.chunk, 0, chunk_len(ch));
 
   // ---- prologue = the previous pass's centroid update (a4), redone by every block:
   //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
@@ -405,7 +428,6 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     }
   }
   __shared__ long long s_scal[KM_ACC_SCALARS];   // block totals: changed, rescored
-  const int lane = threadIdx.x & 31;
   if (threadIdx.x < KM_ACC_SCALARS) s_scal[threadIdx.x] = 0;
   const bool publish = blockIdx.x == 0 && pend && ps.slot != nullptr;
   KmBlockTab T;
@@ -489,20 +511,19 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 
   int changed = 0, rescored = 0;
 
-  for (int64_t ch = blockIdx.x; ch < p.nchunks; ch += gridDim.x) {
+  while (ch < p.nchunks) {
   const int cn = chunk_len(ch);
   const float *__restrict__ xb = p.x + ch * p.chunk * D;
   int32_t *__restrict__ lb = p.labels + ch * p.chunk;
-  const int64_t ch_next = ch + gridDim.x;
   for (int r0 = 0; r0 < cn; r0 += per_round) {
     // software pipeline: the next round's loads (the next chunk's first, at the end of this
     // one) are in flight during this round's arithmetic
     KmBatch<D> nxt;
-    if (!EARLY_LABELS) km_load_labels<D>(cur, lb, r0, cn);
+    if (!EARLY_LABELS) km_load_labels<D, WQ>(cur, lb, r0, cn);
     if (r0 + per_round < cn) {
-      km_load_batch<D, EARLY_LABELS>(nxt, xb, lb, r0 + per_round, cn);
+      km_load_batch<D, EARLY_LABELS, WQ>(nxt, xb, lb, r0 + per_round, cn);
     } else if (ch_next < p.nchunks) {
-      km_load_batch<D, EARLY_LABELS>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
+      km_load_batch<D, EARLY_LABELS, WQ>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
     }
 
     // ---- binary32 filter, top-2 on integer keys
@@ -674,7 +695,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 #pragma unroll
         for (int q = 0; q < PPT; q++) {
           bool live = true;
-          if (!FULL) live = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV) < cn;
+          if (!FULL) live = r0 + km_slot<NV, PPV, WQ>(q / PPV) + (q % PPV) < cn;
           int lab = (int)(m1[q] & mask);
           float xr[D];
 #pragma unroll
@@ -704,7 +725,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 #pragma unroll
       for (int q = 0; q < PPT; q++) {
         bool live = true;
-        if (!FULL) live = r0 + ((q / PPV) * KM_SMALL_THREADS + (int)threadIdx.x) * PPV + (q % PPV) < cn;
+        if (!FULL) live = r0 + km_slot<NV, PPV, WQ>(q / PPV) + (q % PPV) < cn;
         const int lab = newlab[q];
         // queue the move (incremental: re-labelled points only; full: every live point)
         const bool push = live && (p.incremental ? (lab != cur.old[q]) : true);
@@ -737,7 +758,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 #pragma unroll
         for (int u = 0; u < PPV; u++) any |= newlab[v * PPV + u] != cur.old[v * PPV + u];
         if (!any) continue;
-        const int i0 = r0 + (v * KM_SMALL_THREADS + (int)threadIdx.x) * PPV;
+        const int i0 = r0 + km_slot<NV, PPV, WQ>(v);
         if (FULL || i0 + PPV <= cn) {
           if constexpr (PPV == 4) {
             *reinterpret_cast<int4 *>(lb + i0) =
@@ -757,6 +778,8 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     if (r0 + per_round <= cn) tail(std::true_type{}); else tail(std::false_type{});
     cur = nxt;
   }
+  ch = ch_next;
+  ch_next = WQ ? grab() : ch_next + gridDim.x;
   }
 
   // whatever is still queued (fewer than 32 entries per warp)
@@ -838,15 +861,15 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   int grid = (int)grid64;
   p.chunk = chunk;
   p.nchunks = grid64;
-  if (PRUNE && p.sorted && a.n >= cap * per_round * 8) {
-    // Cell-sorted points: how many candidates a point has depends on where it lies, so equal
-    // contiguous shares are not equal work.  Cut the shard into ~32 chunks per block (whole
-    // rounds each) and deal them round-robin: every block gets a sample of the whole plane.
-    int64_t ch = (a.n + cap * 32 - 1) / (cap * 32);
-    ch = (ch + per_round - 1) / per_round * per_round;
-    p.chunk = ch;
-    p.nchunks = (a.n + ch - 1) / ch;
-    grid = (int)(p.nchunks < cap ? p.nchunks : cap);
+  p.work_counter = a.work_counter;
+  if (SORTED) {
+    // units of 16 warp-rounds (2048 points at d = 2), taken dynamically by the warps of one resident wave
+    const int64_t unit = (int64_t)32 * KmSmallCfg<D>::PPT * 16;
+    p.chunk = unit;
+    p.nchunks = (a.n + unit - 1) / unit;
+    const int64_t warps_wanted = p.nchunks < 1 ? 1 : p.nchunks;
+    const int64_t blocks_wanted = (warps_wanted + KM_SMALL_THREADS / 32 - 1) / (KM_SMALL_THREADS / 32);
+    grid = (int)(blocks_wanted < cap ? blocks_wanted : cap);
   }
   p.scale_a = a.scale_a;
   p.scale_b = a.scale_b;
@@ -856,7 +879,7 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
     // this pass's candidate words, for every cell, in front of the assignment kernel
     const int cellsn = a.pr.gp * a.pr.gp;
     km_prune_grid_kernel<<<(cellsn + KM_GRID_THREADS / 32 - 1) / (KM_GRID_THREADS / 32), KM_GRID_THREADS,
-                           (size_t)a.k * 2 * sizeof(float), a.stream>>>(a.ps, a.k, a.pr, p.cboundf, a.cells_g);
+                           (size_t)a.k * 2 * sizeof(float), a.stream>>>(a.ps, a.k, a.pr, p.cboundf, a.cells_g, p.work_counter);
     (*launches)++;
   }
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
@@ -870,7 +893,7 @@ static cudaError_t dispatch_small(const KmAssignArgs &a, int64_t *launches) {
     case 1: return launch_small<1, HILO, false, false>(a, launches);
     case 2:
       if (!a.prune) return launch_small<2, HILO, false, false>(a, launches);
-      return (a.sorted && a.cells_g) ? launch_small<2, HILO, true, true>(a, launches) : launch_small<2, HILO, true, false>(a, launches);
+      return (a.sorted && a.cells_g && a.work_counter) ? launch_small<2, HILO, true, true>(a, launches) : launch_small<2, HILO, true, false>(a, launches);
     case 3: return launch_small<3, HILO, false, false>(a, launches);
     case 4: return launch_small<4, HILO, false, false>(a, launches);
     case 5: return launch_small<5, HILO, false, false>(a, launches);
@@ -889,13 +912,17 @@ cudaError_t km_launch_assign_small(const KmAssignArgs &a, int64_t *launches) {
 
 // d == 2 candidate grid for this job's bounding box; false = do not prune this shape
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
-                          KmPrune2 *out) {
+                          int fine, KmPrune2 *out) {
   if (d != 2 || k < 16 || k > 256) return false;
   // below ~32 points per thread the per-block grid build would not pay off
   const int64_t need = min_points > 0 ? min_points : (int64_t)sm_count * 2 * KM_SMALL_THREADS * 32;
   if (n_local < need) return false;
   int g = 16;
   while (g < 64 && g * g < 64 * k) g *= 2;   // ~8 cells across a Voronoi cell, capped by shared memory
+  // Cell-sorted store (`fine`): the words live in global memory, so the grid may be finer — more cells see a
+  // single candidate — as long as a cell's run of points stays long against a warp-round (>= 4096 on average).
+  if (fine)
+    while (g < 256 && (int64_t)(2 * g) * (2 * g) * 4096 <= n_local) g *= 2;
   const double wx = bbox[1] - bbox[0], wy = bbox[3] - bbox[2];
   if (!(wx > 0.0) || !(wy > 0.0)) return false;
   const double sx = g / (wx * (1.0 + 1e-6)), sy = g / (wy * (1.0 + 1e-6));

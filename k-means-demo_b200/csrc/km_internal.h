@@ -138,6 +138,7 @@ struct KmAssignArgs {
   KmPrune2 pr;
   int sorted;          // ... and the points are stored in ascending cell order of `pr`
   unsigned long long *cells_g;   // ... with room for one candidate word per cell (km_prune_grid_kernel)
+  unsigned *work_counter;        // ... and a counter the assignment kernel's warps take their units of work from
   cudaStream_t stream;
 };
 
@@ -151,7 +152,8 @@ size_t km_tensor_h_bytes(int32_t k);
 size_t km_tensor_work_bytes(int64_t n);
 cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
-                          KmPrune2 *out);
+                          int fine, KmPrune2 *out);
+#define KM_PRUNE_MAX_GP 260   // finest grid side (256 cells + margins)
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 
 cudaError_t km_launch_scan(const void *x, int dtype, int64_t count, double *maxabs_out /*device*/,
