@@ -103,12 +103,14 @@ def measured_peak_gbs():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic_bytes(workload):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the assignment kernel, from
-    the committed `ncu --set full` capture (profiles/ncu_traffic.json), or None."""
+def ncu_traffic_bytes(workload, n_local):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the assignment kernel: the
+    per-point figure of the committed `ncu --set full` capture (profiles/ncu_traffic.json)
+    times the points this launch processes, or None."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            return json.load(f).get(workload, {}).get("dram_bytes_per_launch")
+            per_point = json.load(f).get(workload, {}).get("dram_bytes_per_point")
+        return None if per_point is None else per_point * n_local
     except Exception:
         return None
 
@@ -309,7 +311,7 @@ def roofline_of(key, wl, n_local, kern_avg_ms, path_name):
         flops = 2.0 * k * d * n_local
         achieved = flops / (kern_avg_ms * 1e-3) / 1e12
         return {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": ncu_traffic_bytes(key),
+                "traffic": ncu_traffic_bytes(key, n_local),
                 "kernel": "km_tensor_coarse_kernel (+ the norm, order and exact-stage kernels of the same assignment)",
                 "kernel_ms": kern_avg_ms, "algorithmic_flops_per_launch": flops, "peak_source": peak_src,
                 "hbm_frac_of_measured": algorithmic_bytes_per_point(d) * n_local / (kern_avg_ms * 1e-3) / 1e9 / measured_peak_gbs()[0]}
@@ -317,7 +319,7 @@ def roofline_of(key, wl, n_local, kern_avg_ms, path_name):
     achieved = alg_bytes / (kern_avg_ms * 1e-3) / 1e9
     peak, peak_src = measured_peak_gbs()
     return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": ncu_traffic_bytes(key),
+            "traffic": ncu_traffic_bytes(key, n_local),
             "kernel": "km_assign_small_kernel" if path_name == "filter_f32" else "km_assign_direct_kernel",
             "kernel_ms": kern_avg_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
             "frac_of_nominal_8TBs": achieved / 8000.0}
