@@ -95,7 +95,8 @@ static void free_points(km_ctx *ctx) {
   if (ctx->x && ctx->own_x) cudaFree(ctx->x);
   if (ctx->labels) cudaFree(ctx->labels);
   if (ctx->perm) cudaFree(ctx->perm);
-  ctx->perm = nullptr; ctx->passes_since_upload = 0;
+  if (ctx->unperm_buf) cudaFree(ctx->unperm_buf);
+  ctx->perm = nullptr; ctx->unperm_buf = nullptr; ctx->passes_since_upload = 0;
   if (ctx->t_work) cudaFree(ctx->t_work);
   if (ctx->t_order) cudaFree(ctx->t_order);
   if (ctx->t_xn) cudaFree(ctx->t_xn);
@@ -576,12 +577,14 @@ extern "C" km_status km_get_points(km_ctx *ctx, void *host, int64_t i0, int64_t 
   if (i0 < 0 || n < 0 || i0 + n > ctx->n || (n > 0 && !host)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_points: range outside the shard");
   size_t row = (size_t)ctx->d * elt_size(ctx->dtype);
   if (ctx->perm && n > 0) {  // stored in cell order: put the requested rows back in the caller's
-    float *tmp = nullptr;
-    KM_CUDA(ctx, cudaMalloc(&tmp, (size_t)n * row));
+    // small requests (a Forgy pick, a prefix) go through the buffer the store keeps for un-permuting labels
+    const bool own = (size_t)n * row > (size_t)ctx->n * sizeof(int32_t) || !ctx->unperm_buf;
+    float *tmp = reinterpret_cast<float *>(ctx->unperm_buf);
+    if (own) KM_CUDA(ctx, cudaMalloc(&tmp, (size_t)n * row));
     cudaError_t e = km_unpermute_rows2((const float *)ctx->x, ctx->perm, ctx->n, i0, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches);
     km_status s = KM_OK;
     if (e == cudaSuccess) s = copy_d2h(ctx, host, tmp, (size_t)n * row);
-    cudaFree(tmp);
+    if (own) cudaFree(tmp);
     KM_CUDA(ctx, e);
     return s;
   }
@@ -913,6 +916,7 @@ static km_status maybe_sort_points(km_ctx *ctx) {
   KM_CUDA(ctx, km_sort_points_by_cell(&x, &ctx->labels, ctx->n, pr, &ctx->perm, ctx->sm_count, ctx->stream, &ctx->launches));
   ctx->x = x;
   ctx->sort_pr = pr;
+  if (!ctx->unperm_buf) KM_CUDA(ctx, cudaMalloc(&ctx->unperm_buf, std::max<size_t>((size_t)ctx->n * sizeof(int32_t), 16)));
   if (!ctx->cells_g) KM_CUDA(ctx, cudaMalloc(&ctx->cells_g, ((size_t)KM_PRUNE_MAX_GP * KM_PRUNE_MAX_GP + 1) * sizeof(unsigned long long)));   // words + the work counter
   return KM_OK;
 }
@@ -1220,14 +1224,11 @@ extern "C" km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n) {
   if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
   if (n != ctx->n || (n > 0 && !out)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_labels: n must equal the shard size");
   if (ctx->perm && n > 0) {
-    int32_t *tmp = nullptr;
-    KM_CUDA(ctx, cudaMalloc(&tmp, (size_t)n * sizeof(int32_t)));
-    cudaError_t e = km_unpermute_labels(ctx->labels, ctx->perm, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches);
-    km_status s = KM_OK;
-    if (e == cudaSuccess) s = copy_d2h(ctx, out, tmp, (size_t)n * sizeof(int32_t));
-    cudaFree(tmp);
-    KM_CUDA(ctx, e);
-    return s;
+    // the cell-sorted store keeps one n-label buffer for this (allocated with the sort): no allocation here
+    if (!ctx->unperm_buf) KM_CUDA(ctx, cudaMalloc(&ctx->unperm_buf, (size_t)n * sizeof(int32_t)));
+    int32_t *tmp = reinterpret_cast<int32_t *>(ctx->unperm_buf);
+    KM_CUDA(ctx, km_unpermute_labels(ctx->labels, ctx->perm, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches));
+    return copy_d2h(ctx, out, tmp, (size_t)n * sizeof(int32_t));
   }
   return copy_d2h(ctx, out, ctx->labels, (size_t)n * sizeof(int32_t));
 }

@@ -10,16 +10,19 @@
 //           their few candidate centroids in the same columns (points never move; only an index
 //           list is rebuilt, and every per-cluster sum is order-free).
 //  coarse   km_tensor_coarse_kernel, warp-specialised, one CTA per SM, 256 points per pass:
-//             4 producer warps  gather the pass's rows of x by the index list, convert to BF16 and
-//                               store them K-major / SWIZZLE_128B (two 128-row tiles, 2 stages);
-//             1 TMA thread      streams 128-centroid tiles of the BF16 copy with
-//                               cp.async.bulk.tensor (2-4 stages, mbarrier complete_tx);
-//             1 MMA thread      tcgen05.mma kind::f16, 2 point tiles x 128 centroids per step into
-//                               4 x 128 TMEM columns (double-buffered), tcgen05.commit -> mbarriers;
+//             6 producer warps  gather the pass's rows of x by the index list, convert to BF16 and
+//                               store them K-major / SWIZZLE_128B (two 128-row tiles, 2-4 stages);
+//             1 TMA warp        an elected lane streams 128-centroid tiles of the BF16 copy with
+//                               cp.async.bulk.tensor (2-4 stages, mbarrier complete_tx), starting
+//                               with the tile that holds the pass's previous label;
+//             1 MMA warp        an elected lane issues tcgen05.mma kind::f16, 2 point tiles x 128
+//                               centroids per step into 4 x 128 TMEM columns (double-buffered),
+//                               tcgen05.commit -> mbarriers;
 //             8 epilogue warps  tcgen05.ld 32 columns at a time; score = x~.c~ - |c|^2/2 (packed
-//                               f32x2 adds), the chunk maximum by 3-input FMNMX; only a chunk whose
-//                               maximum comes within the BF16 error window of the running maximum
-//                               is looked at column by column.
+//                               f32x2 adds of h from shared memory, or nothing at all when h rides
+//                               in the contraction), the chunk maximum by 3-input FMNMX; only a
+//                               chunk whose maximum comes within the BF16 error window of the
+//                               running maximum is looked at column by column.
 //           The N x k matrix never exists.  A point whose only survivor is its previous label is
 //           finished right there (nothing is written for it: the inertia comes from the sums);
 //           every other point goes to a compact worklist with up to 8 survivors.

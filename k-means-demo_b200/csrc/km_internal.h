@@ -36,6 +36,7 @@ struct km_ctx {
   int32_t *labels = nullptr;  // device, n
   unsigned *perm = nullptr;   // device, n: original row of each stored row once the store was cell-sorted (km_sort.cu)
   unsigned long long *cells_g = nullptr;   // device: candidate word per grid cell of the sorted store (rebuilt every pass)
+  void *unperm_buf = nullptr; // device, n labels: where km_get_labels / small km_get_points put rows back in the caller's order
   KmPrune2 sort_pr;           // the grid the stored order follows
   int passes_since_upload = 0;
   void *pinned = nullptr;     // staging for uploads / downloads
