@@ -72,8 +72,8 @@ typedef struct km_config {
   int32_t device;      /* CUDA ordinal */
   int32_t path;        /* KM_PATH_* */
   int32_t update_mode; /* KM_UPDATE_* */
-  int32_t exact_inertia; /* 1: inertia from binary64 winner distances (<=1e-9 rel);
-                            0: from the filter's binary32 distances (<=1e-5 rel) */
+  int32_t exact_inertia; /* kept for layout compatibility and ignored: the inertia always comes from the
+                            order-free sums (exact to ~1e-15 relative, identical at any GPU count) */
   int32_t profile_kernels; /* 1: bracket each assignment kernel with CUDA events (km_kernel_time) */
   void *stream;        /* cudaStream_t to run on, or NULL for a private stream */
   int32_t no_prune;    /* 1: never use the d = 2 candidate grid (brute force over all k) */
@@ -109,6 +109,11 @@ KM_API km_status km_host_free(void *p);
 /* 128-byte NCCL unique id: rank 0 produces it, the host layer broadcasts it */
 KM_API km_status km_comm_unique_id(void *out128);
 /* join a communicator of `world` ranks.  Must precede km_upload_points/km_generate_blobs.
+ * From then on km_upload_points / km_generate_blobs / km_attach_points, the km_init_* calls, every
+ * assign / step / run and km_get_cluster_inertia are COLLECTIVE: every rank must make the same
+ * calls in the same order.  A rank whose call fails locally (CUDA error, out of memory) returns
+ * its error before joining the collective, and the other ranks then wait in NCCL: treat any
+ * non-zero status on one rank as fatal for the job and tear all ranks down.
  * replaces: the P2PT/WebRTC gossip of UI state (app.mjs:70-118) only in the sense that it
  * is the reference's sole inter-process link; it is not a compute collective there. */
 KM_API km_status km_comm_init(km_ctx *ctx, const void *id128, int32_t rank, int32_t world);
@@ -138,8 +143,10 @@ KM_API km_status km_init_kmeanspp(km_ctx *ctx, int32_t k, uint64_t seed);
 
 /* ---- a3: assignment step (analog: updateCardAssign app.mjs:146-156, drop :358-372) -- */
 /* label[i] = argmin_j sum_t (x_it - c_jt)^2, strict <, lowest j wins ties; also counts
- * changed labels, sums the winner distances, and moves each re-labelled point between the
- * per-cluster sums (the update's partial sums are fused into this pass). */
+ * changed labels and moves each re-labelled point between the per-cluster sums (the update's
+ * partial sums are fused into this pass); the sum of the winner distances (km_stats.inertia)
+ * follows from those sums.  Kernel family by shape (KM_PATH_AUTO): d <= 8 the binary32 filter,
+ * 9 <= d <= 128 with k >= 16 the tcgen05 tensor path, anything else binary64 brute force. */
 KM_API km_status km_assign(km_ctx *ctx, km_stats *stats);
 
 /* ---- a4: centroid-update step (analog: traitCountsFor/suggestionFromCounts/
