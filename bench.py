@@ -445,6 +445,7 @@ def measure(job, key, wl, steps, warmup, burn_s, keep_state=False):
         "roofline": roofline_of(key, wl, n, kern_avg_ms, path_name), "gpu_launches": launches,
         "changed_at_last_step": last["changed"], "parity_check": parity,
         "step_ms_min_med_max": [min(step_ms), statistics.median(step_ms), max(step_ms)],
+        "step_ms": [round(v, 4) for v in step_ms],
     }
     extra = dict(st=st, c0=c0, n=n, lo=lo, t_load=(t_load0, t_load1), total_ms=total_ms, launches=launches)
     if not keep_state:
@@ -558,7 +559,7 @@ def run_ours(args, wl):
                         "changed_at_last_step": main["changed_at_last_step"]},
             "roofline": main["roofline"], "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": main["gpu_launches"], "clocks": clocks,
             "first_pass_ms": main["first_pass_ms"], "full_mode_ms_per_step": main["full_mode_ms_per_step"],
-            "step_ms_min_med_max": main["step_ms_min_med_max"],
+            "step_ms_min_med_max": main["step_ms_min_med_max"], "step_ms": main["step_ms"],
             "parity_check": parity, "parity_check_after_3_iterations": main["parity_check"],
             "shapes": shapes,
         }
