@@ -56,7 +56,8 @@ enum { KM_DTYPE_F32 = 0, KM_DTYPE_F64 = 1 };
 /* which assignment kernel family runs (km_config.path) */
 enum {
   KM_PATH_AUTO = 0,       /* pick by (d, k) */
-  KM_PATH_DIRECT_F64 = 1, /* every distance in binary64, the oracle's exact op order */
+  KM_PATH_DIRECT_F64 = 1, /* every distance in binary64, the oracle's exact op order (d up to ~28 000:
+                             one centroid row must fit shared memory; km_set_centroids says so otherwise) */
   KM_PATH_FILTER_F32 = 2, /* binary32 distances + error-bound test + binary64 re-score */
   KM_PATH_TENSOR = 3      /* tcgen05 GEMM-form distances + error-bound test + re-score */
 };

@@ -610,6 +610,11 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
     return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_FILTER_F32 needs float32 points, d <= 8, k <= 4096, k*d <= 8192");
   if (path == KM_PATH_TENSOR && !km_tensor_path_supported(d, k, ctx->dtype, ctx->max_smem_optin))
     return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_TENSOR needs float32 points, 9 <= d <= 128, k >= 2");
+  // binary64 brute force stages one centroid row (d doubles) in shared memory: say so here, not as an opaque
+  // launch failure at the first assign
+  if (path == KM_PATH_DIRECT_F64 && (size_t)d * sizeof(double) + 4096 > (size_t)ctx->max_smem_optin)
+    return fail(ctx, KM_ERR_UNSUPPORTED, "KM_PATH_DIRECT_F64 needs d * 8 bytes of shared memory per centroid row: d <= " +
+                                             std::to_string((ctx->max_smem_optin - 4096) / 8) + " on this device");
   const bool p1 = path == KM_PATH_FILTER_F32;
   if (!ctx->have_centroids || ctx->k != k || ctx->acc_len != L.len || ctx->p1 != p1 || ctx->path_now != path) {
     free_centroids(ctx);
