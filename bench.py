@@ -446,6 +446,8 @@ def measure(job, key, wl, steps, warmup, burn_s, keep_state=False):
         "changed_at_last_step": last["changed"], "parity_check": parity,
         "step_ms_min_med_max": [min(step_ms), statistics.median(step_ms), max(step_ms)],
         "step_ms": [round(v, 4) for v in step_ms],
+        "collective": "none (one rank)" if world == 1 else
+                      ("one-shot kernel over peer memory" if st.comm_info()[2] == 2 else "ncclAllReduce(int64)"),
     }
     extra = dict(st=st, c0=c0, n=n, lo=lo, t_load=(t_load0, t_load1), total_ms=total_ms, launches=launches)
     if not keep_state:
@@ -553,7 +555,7 @@ def run_ours(args, wl):
             "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": main["scaling"], "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": config,
             "details": {"n_per_gpu": n, "arithmetic": "binary32 filter + binary64 re-score, int64 order-free sums, inertia from the sums",
-                        "path": main["path"], "update_mode": "incremental",
+                        "path": main["path"], "update_mode": "incremental", "collective": main["collective"],
                         "l2": "NOT flushed (diagnostic run, invalid as a bench value)" if args.no_flush else "flushed between timed steps (256 MiB write)",
                         "timed_iterations": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} from the seeded init",
                         "changed_at_last_step": main["changed_at_last_step"]},

@@ -89,6 +89,12 @@ class KMeansState:
         self._check(self._lib.km_comm_init(self._h, buf, rank, world))
         self.rank, self.world = rank, world
 
+    def comm_info(self):
+        """(rank, world, peer_allreduce): 0 = NCCL only, 1 = peer regions mapped, 2 = in use by the installed tables."""
+        r, w, p = C.c_int32(0), C.c_int32(1), C.c_int32(0)
+        self._check(self._lib.km_comm_info(self._h, C.byref(r), C.byref(w), C.byref(p)))
+        return r.value, w.value, p.value
+
     # -- a1: store
     def upload_points(self, points):
         x = np.ascontiguousarray(points)

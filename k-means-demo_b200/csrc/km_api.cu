@@ -112,7 +112,12 @@ static void free_centroids(km_ctx *ctx) {
   if (ctx->acc) cudaFree(ctx->acc);
   ctx->c64 = nullptr; ctx->chi = ctx->clo = nullptr; ctx->acc = ctx->acc_global = nullptr;
   for (int q = 0; q < 2; q++) { if (ctx->p1S[q]) cudaFree(ctx->p1S[q]); if (ctx->p1C[q]) cudaFree(ctx->p1C[q]); ctx->p1S[q] = nullptr; ctx->p1C[q] = nullptr; }
-  for (int q = 0; q < 3; q++) { if (ctx->p1D[q]) cudaFree(ctx->p1D[q]); ctx->p1D[q] = nullptr; }
+  for (int q = 0; q < 3; q++) {
+    if (ctx->p1D[q] && !ctx->p1D_in_peer) cudaFree(ctx->p1D[q]);
+    if (ctx->p1R[q]) cudaFree(ctx->p1R[q]);
+    ctx->p1D[q] = ctx->p1R[q] = nullptr;
+  }
+  ctx->p1D_in_peer = false;
   if (ctx->t_cn) cudaFree(ctx->t_cn);
   if (ctx->t_cbf) cudaFree(ctx->t_cbf);
   if (ctx->t_hist) cudaFree(ctx->t_hist);
@@ -253,12 +258,17 @@ static km_status push_state(km_ctx *ctx) {
   return KM_OK;
 }
 
+static km_status peer_barrier(km_ctx *ctx);
 static km_status reset_labels(km_ctx *ctx) {
   if (ctx->labels) KM_CUDA(ctx, km_launch_fill_i32(ctx->labels, ctx->n, -1, ctx->sm_count, ctx->stream, &ctx->launches));
   if (ctx->acc) KM_CUDA(ctx, cudaMemsetAsync(ctx->acc, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
   if (ctx->acc_global && ctx->acc_global != ctx->acc)
     KM_CUDA(ctx, cudaMemsetAsync(ctx->acc_global, 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
   if (ctx->p1) {
+    if (ctx->p1D_in_peer) {  // a peer may still be summing the last pass's table
+      km_status bs = peer_barrier(ctx);
+      if (bs != KM_OK) return bs;
+    }
     for (int q = 0; q < 2; q++) KM_CUDA(ctx, cudaMemsetAsync(ctx->p1S[q], 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
     for (int q = 0; q < 3; q++) KM_CUDA(ctx, cudaMemsetAsync(ctx->p1D[q], 0, (size_t)ctx->acc_len * sizeof(long long), ctx->stream));
     ctx->p1_pending = false;
@@ -465,6 +475,95 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   return KM_OK;
 }
 
+// ------------------------------------------------------------------ peer regions (km_peer.cu)
+// Each rank allocates one region, the ranks exchange CUDA IPC handles through the communicator and
+// map each other's.  Any failure on any rank (ranks on different nodes, no peer access, IPC
+// unavailable) leaves every rank on the NCCL all-reduce: the decision is itself all-reduced.
+static void peer_teardown(km_ctx *ctx) {
+  for (int r = 0; r < KM_PEER_MAX_WORLD; r++) {
+    if (!ctx->peer_base[r]) continue;
+    if (r == ctx->rank) cudaFree(ctx->peer_base[r]);
+    else cudaIpcCloseMemHandle(ctx->peer_base[r]);
+    ctx->peer_base[r] = nullptr;
+  }
+  if (ctx->peer_err) cudaFreeHost(ctx->peer_err);
+  ctx->peer_err = nullptr;
+  ctx->peer_ok = false;
+  cudaGetLastError();
+}
+
+static km_status peer_setup(km_ctx *ctx) {
+  ctx->peer_ok = false;
+  if (ctx->world < 2 || ctx->world > KM_PEER_MAX_WORLD) return KM_OK;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle travels as 8 int64");
+  const int W = ctx->world, NH = 9;  // 8 words of handle + "this rank is fine so far"
+  const size_t alloc_bytes = 2u << 20;  // a whole allocation block of its own, so the handle maps exactly this pointer
+  static_assert(KM_PEER_REGION_BYTES <= (2u << 20), "region fits its allocation");
+  bool ok = true;
+  void *base = nullptr;
+  ok = cudaMalloc(&base, alloc_bytes) == cudaSuccess && cudaMemset(base, 0, alloc_bytes) == cudaSuccess &&
+       cudaDeviceSynchronize() == cudaSuccess;
+  ctx->peer_base[ctx->rank] = ok ? base : nullptr;
+  long long h_in[NH];
+  memset(h_in, 0, sizeof(h_in));
+  cudaIpcMemHandle_t mine;
+  if (ok) ok = cudaIpcGetMemHandle(&mine, base) == cudaSuccess;
+  if (ok) memcpy(h_in, &mine, sizeof(mine));
+  if (ok) ok = cudaHostAlloc(&ctx->peer_err, sizeof(int), cudaHostAllocMapped) == cudaSuccess;
+  if (ok) *ctx->peer_err = 0;
+  h_in[8] = ok ? 1 : 0;
+  cudaGetLastError();
+  // the two collectives below are joined by every rank whatever happened above
+  long long *d_buf = nullptr;
+  std::vector<long long> h_out((size_t)NH * W);
+  KM_CUDA(ctx, cudaMalloc(&d_buf, sizeof(long long) * NH * (W + 1)));
+  cudaError_t e = cudaMemcpyAsync(d_buf, h_in, sizeof(h_in), cudaMemcpyHostToDevice, ctx->stream);
+  int rc = g_nccl.all_gather(d_buf, d_buf + NH, NH, KM_NCCL_INT64, ctx->nccl_comm, ctx->stream);
+  if (e == cudaSuccess && rc == 0)
+    e = cudaMemcpyAsync(h_out.data(), d_buf + NH, h_out.size() * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(ctx->stream);
+  if (rc != 0 || e != cudaSuccess) {
+    cudaFree(d_buf);
+    peer_teardown(ctx);
+    if (rc != 0) return fail(ctx, KM_ERR_NCCL, std::string("ncclAllGather: ") + g_nccl.get_error_string(rc));
+    return fail(ctx, KM_ERR_CUDA, cudaGetErrorString(e));
+  }
+  for (int r = 0; r < W; r++) ok = ok && h_out[(size_t)NH * r + 8] == 1;
+  for (int r = 0; r < W && ok; r++) {
+    if (r == ctx->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, &h_out[(size_t)NH * r], sizeof(h));
+    void *p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; cudaGetLastError(); break; }
+    ctx->peer_base[r] = p;
+  }
+  long long bad = ok ? 0 : 1;
+  e = cudaMemcpyAsync(d_buf, &bad, sizeof(bad), cudaMemcpyHostToDevice, ctx->stream);
+  rc = g_nccl.all_reduce(d_buf, d_buf, 1, KM_NCCL_INT64, KM_NCCL_SUM, ctx->nccl_comm, ctx->stream);
+  if (e == cudaSuccess && rc == 0) e = cudaMemcpyAsync(&bad, d_buf, sizeof(bad), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_buf);
+  if (rc != 0 || e != cudaSuccess || bad != 0) {
+    peer_teardown(ctx);
+    if (rc != 0) return fail(ctx, KM_ERR_NCCL, std::string("ncclAllReduce: ") + g_nccl.get_error_string(rc));
+    if (e != cudaSuccess) return fail(ctx, KM_ERR_CUDA, cudaGetErrorString(e));
+    return KM_OK;  // some rank could not map a peer: everybody stays on NCCL
+  }
+  ctx->peer_ok = true;
+  ctx->peer_epoch = 0;
+  return KM_OK;
+}
+
+// every rank has finished reading every table published so far (needed before a table is
+// cleared outside the three-pass rotation)
+static km_status peer_barrier(km_ctx *ctx) {
+  if (!ctx->peer_ok) return KM_OK;
+  ctx->peer_epoch++;
+  KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, 0, 0, ctx->peer_epoch, nullptr, ctx->peer_err,
+                                        ctx->stream, &ctx->launches));
+  return KM_OK;
+}
+
 extern "C" km_status km_destroy(km_ctx *ctx) {
   if (!ctx) return KM_OK;
   cudaSetDevice(ctx->device);
@@ -472,6 +571,7 @@ extern "C" km_status km_destroy(km_ctx *ctx) {
   if (ctx->nccl_comm && g_nccl.comm_destroy) g_nccl.comm_destroy(ctx->nccl_comm);
   free_points(ctx);
   free_centroids(ctx);
+  peer_teardown(ctx);
   if (ctx->state) cudaFree(ctx->state);
   if (ctx->scan_max) cudaFree(ctx->scan_max);
   if (ctx->scan_bad) cudaFree(ctx->scan_bad);
@@ -527,6 +627,14 @@ extern "C" km_status km_comm_init(km_ctx *ctx, const void *id128, int32_t rank, 
   KM_NCCL(ctx, g_nccl.comm_init_rank(&ctx->nccl_comm, world, id, rank));
   ctx->rank = rank;
   ctx->world = world;
+  return peer_setup(ctx);
+}
+
+extern "C" km_status km_comm_info(const km_ctx *ctx, int32_t *rank, int32_t *world, int32_t *peer_allreduce) {
+  if (!ctx) return KM_ERR_INVALID_ARG;
+  if (rank) *rank = ctx->rank;
+  if (world) *world = ctx->world;
+  if (peer_allreduce) *peer_allreduce = !ctx->peer_ok ? 0 : (ctx->p1D_in_peer ? 2 : 1);
   return KM_OK;
 }
 
@@ -625,7 +733,14 @@ static km_status install_centroids(km_ctx *ctx, const double *c_host, int32_t k)
         KM_CUDA(ctx, cudaMalloc(&ctx->p1S[q], (size_t)L.len * sizeof(long long)));
         KM_CUDA(ctx, cudaMalloc(&ctx->p1C[q], kd * sizeof(double)));
       }
-      for (int q = 0; q < 3; q++) KM_CUDA(ctx, cudaMalloc(&ctx->p1D[q], (size_t)L.len * sizeof(long long)));
+      // tables small enough for the one-shot peer all-reduce live in the region the peers have mapped
+      ctx->p1D_in_peer = ctx->peer_ok && (size_t)L.len * sizeof(long long) <= KM_PEER_TABLE_BYTES;
+      for (int q = 0; q < 3; q++) {
+        if (ctx->p1D_in_peer) {
+          ctx->p1D[q] = reinterpret_cast<long long *>(static_cast<unsigned char *>(ctx->peer_base[ctx->rank]) + (size_t)q * KM_PEER_TABLE_BYTES);
+          KM_CUDA(ctx, cudaMalloc(&ctx->p1R[q], (size_t)L.len * sizeof(long long)));
+        } else KM_CUDA(ctx, cudaMalloc(&ctx->p1D[q], (size_t)L.len * sizeof(long long)));
+      }
       ctx->p1 = true;
       ctx->p1_s = 0;
     } else {
@@ -784,8 +899,8 @@ extern "C" km_status km_init_kmeanspp(km_ctx *ctx, int32_t k, uint64_t seed) {
   auto cleanup = [&]() { if (D) cudaFree(D); if (c_dev) cudaFree(c_dev); if (partial) cudaFree(partial); if (small) cudaFree(small); };
 #define KM_PP_CUDA(expr)                                                          \
   do {                                                                            \
-    cudaError_t _e = (expr);                                                      \
-    if (_e != cudaSuccess) { cleanup(); KM_CUDA(ctx, _e); }                       \
+    cudaError_t _pe = (expr);                                                     \
+    if (_pe != cudaSuccess) { cleanup(); KM_CUDA(ctx, _pe); }                     \
   } while (0)
   KM_PP_CUDA(cudaMalloc(&D, std::max<size_t>((size_t)n * sizeof(double), 16)));
   KM_PP_CUDA(cudaMalloc(&c_dev, (size_t)d * sizeof(double)));
@@ -1001,7 +1116,8 @@ static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
   const int s = ctx->p1_s;
   ps.S_in = ctx->p1S[s]; ps.S_out = ctx->p1S[s ^ 1];
   ps.C_in = ctx->p1C[s]; ps.C_out = ctx->p1C[s ^ 1];
-  ps.D_in = ctx->p1_pending ? ctx->p1D[ctx->p1_dpend] : nullptr;
+  // D_in: the job-wide table — the peer all-reduce leaves it in p1R, NCCL (and one rank) in place
+  ps.D_in = ctx->p1_pending ? (ctx->p1D_in_peer ? ctx->p1R[ctx->p1_dpend] : ctx->p1D[ctx->p1_dpend]) : nullptr;
   ps.D_out = ctx->p1D[ctx->p1_dw];
   ps.D_zero = assign ? ctx->p1D[(ctx->p1_dw + 1) % 3] : nullptr;
   ps.slot = ctx->p1_pending ? ctx->ring_dev + (ctx->p1_pend_it % KM_RING) : nullptr;
@@ -1024,7 +1140,12 @@ static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
   ctx->p1_pending = false;
   ctx->last_path = KM_PATH_FILTER_F32;
   if (assign) {
-    if (ctx->world > 1)  // the one collective of an iteration: the packed deltas, in place
+    if (ctx->p1D_in_peer) {  // the one collective of an iteration: one small kernel over peer memory
+      ctx->peer_epoch++;
+      KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, (size_t)ctx->p1_dw * KM_PEER_TABLE_BYTES,
+                                            ctx->acc_len, ctx->peer_epoch, ctx->p1R[ctx->p1_dw], ctx->peer_err, ctx->stream,
+                                            &ctx->launches));
+    } else if (ctx->world > 1)  // ... or NCCL, in place
       KM_NCCL(ctx, g_nccl.all_reduce(ps.D_out, ps.D_out, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
                                      ctx->nccl_comm, ctx->stream));
     ctx->host_it += 1;
@@ -1070,6 +1191,8 @@ static void fill_stats(km_ctx *ctx, const KmStatSlot &s, km_stats *out, float ms
 static km_status wait_slot(km_ctx *ctx, int32_t it, KmStatSlot *out) {
   KM_CUDA(ctx, cudaEventSynchronize(ctx->ring_ev[it % KM_RING]));
   *out = ctx->ring[it % KM_RING];
+  if (ctx->peer_err && *reinterpret_cast<volatile int *>(ctx->peer_err))
+    return fail(ctx, KM_ERR_NCCL, "peer all-reduce: a rank did not arrive within the time limit");
   if (out->it != it) return fail(ctx, KM_ERR_STATE, "stats ring overrun");
   // filter escalation: hi-only binary32 centroids carry an absolute error ~ d*u*max|c|^2; when
   // that sends more than 2% of the job to the binary64 re-score, switch to hi/lo pairs

@@ -8,6 +8,11 @@
 #include "km_common.cuh"
 #include "km_finalize.cuh"
 
+// peer all-reduce region: three rotating tables, then one epoch flag per rank
+#define KM_PEER_MAX_WORLD 16
+#define KM_PEER_TABLE_BYTES (64 * 1024)
+#define KM_PEER_FLAGS_OFF (3 * KM_PEER_TABLE_BYTES)
+#define KM_PEER_REGION_BYTES (KM_PEER_FLAGS_OFF + 4096)
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
 #define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
@@ -87,6 +92,14 @@ struct km_ctx {
   int p1_pend_update = 0, p1_pend_nc = 0;  // ... to be applied with this intent
   int32_t p1_pend_it = 0;
 
+  // ---- peer all-reduce of the small-d tables (km_peer.cu); set up in km_comm_init
+  bool peer_ok = false;             // every rank mapped every peer's region
+  void *peer_base[KM_PEER_MAX_WORLD] = {};   // regions as mapped in this process; [rank] is this rank's own allocation
+  bool p1D_in_peer = false;         // p1D[] point into peer_base[rank] (not separately allocated)
+  long long *p1R[3] = {nullptr, nullptr, nullptr};  // the summed tables the next pass reads
+  unsigned long long peer_epoch = 0;
+  int *peer_err = nullptr;          // mapped pinned host word: a peer never arrived
+
   // ---- tensor path scratch
   float *t_cn = nullptr;            // -|chi_j|^2 / 2 per (padded) centroid
   void *t_cbf = nullptr;            // BF16 copy of the centroids
@@ -154,6 +167,8 @@ size_t km_tensor_work_bytes(int64_t n);
 cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           int fine, KmPrune2 *out);
+cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, int64_t len,
+                                     unsigned long long epoch, long long *out, int *err, cudaStream_t s, int64_t *launches);
 #define KM_PRUNE_MAX_GP 260   // finest grid side (256 cells + margins)
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 

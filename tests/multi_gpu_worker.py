@@ -27,6 +27,7 @@ def main():
     cases = [  # n, d, k, path, update_mode
         (200_003, 2, 8, km._lib.PATH_AUTO, 0), (200_003, 2, 8, km._lib.PATH_AUTO, 1),
         (50_001, 3, 5, km._lib.PATH_DIRECT_F64, 0), (9_000, 32, 16, km._lib.PATH_AUTO, 0), (64_000, 2, 64, km._lib.PATH_AUTO, 0),
+        (20_000, 8, 700, km._lib.PATH_AUTO, 0),   # small-d path with a 95 KB table: above the peer all-reduce's limit, NCCL
     ]
     for ci, (n, d, k, path, mode) in enumerate(cases):
         if rank == 0:
@@ -41,6 +42,20 @@ def main():
             cpp = st.centroids()
             st.init_forgy(k, 11)
             c0 = st.centroids()
+            s = st.run(40)
+            how = st.comm_info()[2]
+            # again from the same start (set_centroids clears the tables: a barrier across the ranks on the peer path),
+            # then single steps with a download in between
+            cent1 = st.centroids()
+            st.set_centroids(c0)
+            s2 = st.run(40)
+            assert s2["iterations"] == s["iterations"] and s2["inertia"] == s["inertia"], (s, s2)
+            assert np.array_equal(st.centroids(), cent1)
+            st.set_centroids(c0)
+            for _ in range(3):
+                st.step()
+                st.labels()
+            st.set_centroids(c0)
             s = st.run(40)
             labels = torch.from_numpy(st.labels()).to(dev)
             cent = st.centroids()
@@ -61,7 +76,8 @@ def main():
             assert np.array_equal(counts, ref["counts"])
             assert abs(s["inertia"] - ref["inertia"]) <= 1e-9 * ref["inertia"]
             assert s["n_total"] == n
-            print(f"case {ci}: world {world} n={n} d={d} k={k} iterations={s['iterations']} ok", flush=True)
+            print(f"case {ci}: world {world} n={n} d={d} k={k} iterations={s['iterations']} "
+                  f"collective={['nccl', 'peer regions mapped, nccl for this table', 'peer kernel'][how]} ok", flush=True)
         dist.barrier()
     if rank == 0:
         print("MULTI_GPU_OK", flush=True)
