@@ -364,7 +364,8 @@ struct KtParams {
 // rare: the survivor list of a point is full.  Drop what the tighter threshold has since excluded;
 // if it is still full keep the KT_LIST best scores and remember the best one that had to go
 // (`lostmax`): the list is complete exactly if that one ends up below the final threshold.
-__device__ __noinline__ int kt_insert_full(int2 *lst, int row, float thr, int col, float val, float &lostmax) {
+// Returns {entries now in the list, lostmax} — by value, so that neither lives in local memory in the caller.
+__device__ __noinline__ int2 kt_insert_full(int2 *lst, int row, float thr, int col, float val, float lostmax) {
   int w = 0;
   for (int s = 0; s < KT_LIST; s++) {
     const int2 e = lst[s * KT_ROWS + row];
@@ -372,7 +373,7 @@ __device__ __noinline__ int kt_insert_full(int2 *lst, int row, float thr, int co
   }
   if (w < KT_LIST) {
     lst[(w++) * KT_ROWS + row] = make_int2(col, __float_as_int(val));
-    return w;
+    return make_int2(w, __float_as_int(lostmax));
   }
   int smin = 0;
   float vmin = __int_as_float(lst[row].y);
@@ -386,7 +387,28 @@ __device__ __noinline__ int kt_insert_full(int2 *lst, int row, float thr, int co
   } else {
     lostmax = fmaxf(lostmax, val);
   }
-  return KT_LIST;
+  return make_int2(KT_LIST, __float_as_int(lostmax));
+}
+
+// rare (a point with more than one recorded column): keep the entries within the window of the FINAL
+// maximum, sort them by centroid index (tie rule: lowest j first) and write the indices back into the
+// list's first slots.  Returns how many (1..8), or -2 when the exact stage has to scan all k: more than
+// eight, a dropped score that the final threshold would have kept, or none at all (a non-finite score).
+__device__ __noinline__ int kt_collect(int2 *lst, int row, int cnt, float thr, float lostmax) {
+  int out[8];
+  int w = 0;
+  for (int s2 = 0; s2 < cnt; s2++) {
+    const int2 e = lst[s2 * KT_ROWS + row];
+    if (__int_as_float(e.y) >= thr) {
+      if (w < 8) out[w] = e.x;
+      w++;
+    }
+  }
+  if (lostmax >= thr || w > 8 || w == 0) return -2;
+  for (int a = 1; a < w; a++)
+    for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
+  for (int s2 = 0; s2 < w; s2++) lst[s2 * KT_ROWS + row].x = out[s2];
+  return w;
 }
 
 // HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
@@ -452,11 +474,10 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     if (ps >= passes || r >= p.n) return -1;
     return p.order ? (int)__ldg(p.order + r) : (int)r;
   };
-  auto start_of = [&](int gi0) -> int {                        // level 2: previous label of a pass's first point
-    if (gi0 < 0) return 0;
-    const int lab = __ldg(p.labels + gi0);
-    return (lab >= 0 && lab < p.k) ? lab : 0;
-  };
+  // level 2: previous label of a pass's first point — the RAW load; it is range-checked (start_ok) only where
+  // it is used, a pass later, so that nothing waits for the load in the pass that issues it
+  auto start_of = [&](int gi0) -> int { return gi0 < 0 ? 0 : __ldg(p.labels + gi0); };
+  auto start_ok = [&](int lab) -> int { return (lab >= 0 && lab < p.k) ? lab : 0; };
 
   if (warp >= KT_EPI_WARPS && warp < KT_WARP_MMA) {
     // ===================== producers: rows of x -> BF16, K-major, swizzled =====================
@@ -527,7 +548,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     int sg1 = idx_at((int64_t)blockIdx.x + gridDim.x, 0);
     int start_next = start_of(idx_at(blockIdx.x, 0));
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x) {
-      const int t0 = start_next / KT_N;
+      const int t0 = start_ok(start_next) / KT_N;
       start_next = start_of(sg1);                               // its index arrived a pass ago
       sg1 = idx_at(ps + 2 * (int64_t)gridDim.x, 0);
       for (int t = 0; t < ntiles; t++, g++) {
@@ -586,7 +607,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     // the score x~.c~ - |c|^2/2 by E/2 with E = (2^-6 + 2^-15) |x||c|.  Survivors: within
     // 2 * E/2 of the best score (plus slack for the fp32 accumulation and the rounding of h).
     // Per point: |x| is its own norm (computed once per upload, rounded up), |c| <= max_j |chi_j|.
-    const float cnmax = sqrtf(p.st->cnmax2);
+    const float cnmax2 = p.st->cnmax2, cnmax = sqrtf(cnmax2);
     const float NEG_INF = __int_as_float(0xff800000);
     uint32_t g = 0;
     int it = 0;
@@ -602,7 +623,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     point_of(gi_next, lab_next, xn_next);
     int start_next = start_of(idx_at(blockIdx.x, 0));
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
-      const int gi = gi_next, lab = lab_next, start = start_next;
+      const int gi = gi_next, lab = lab_next, start = start_ok(start_next);
       const bool live = gi >= 0;
       const float xn = fminf(xn_next * 1.0001f, p.xnmax);      // |x_i| (km_row_norm_kernel), rounded up
       gi_next = gi_n2;
@@ -611,7 +632,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
       gi_n2 = idx_at(ps + 2 * (int64_t)gridDim.x, row);
       sg1 = idx_at(ps + 2 * (int64_t)gridDim.x, 0);
       const int t0 = start / KT_N, c0 = (start % KT_N) >> 5;   // first tile, and the first chunk within it
-      const float win = 0.0156556f * xn * cnmax + 1e-6f * (xn * xn + p.st->cnmax2);
+      const float win = 0.0156556f * xn * cnmax + 1e-6f * (xn * xn + cnmax2);
       float runmax = NEG_INF, thr = NEG_INF;
       int cnt = 0;
       float lostmax = NEG_INF;                // best score the full list had to let go
@@ -666,7 +687,11 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
           }
           if ((mask >> i) & 1u) {
             if (cnt < KT_LIST) lst[(cnt++) * KT_ROWS + row] = make_int2(col0 + i, __float_as_int(val));
-            else cnt = kt_insert_full(lst, row, thr, col0 + i, val, lostmax);
+            else {
+              const int2 r2 = kt_insert_full(lst, row, thr, col0 + i, val, lostmax);
+              cnt = r2.x;
+              lostmax = __int_as_float(r2.y);
+            }
           }
         }
       };
@@ -701,27 +726,14 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         chunk(vb, tt * KT_N + q3);
       }
 
-      // ---- survivors of this point: within the window of the final maximum, ascending index
-      int out[8];
-      int w = 0;
-      for (int s2 = 0; s2 < cnt; s2++) {
-        const int2 e = lst[s2 * KT_ROWS + row];
-        if (__int_as_float(e.y) >= thr) {
-          if (w < 8) out[w] = e.x;
-          w++;
-        }
-      }
-      int nout = w;
-      if (lostmax >= thr || w > 8 || w == 0) {
-        nout = -2;                           // too many to list (or a non-finite score): the exact stage scans all k
-        for (int s2 = 0; s2 < 8; s2++) out[s2] = -1;
-      } else {
-        for (int s2 = w; s2 < 8; s2++) out[s2] = -1;
-        for (int a = 1; a < w; a++)          // insertion sort, ascending index (tie rule: lowest j first)
-          for (int q = a; q > 0 && out[q] < out[q - 1]; q--) { const int tmp = out[q]; out[q] = out[q - 1]; out[q - 1] = tmp; }
-      }
+      // ---- survivors of this point: within the window of the final maximum, ascending index.
+      // Nearly always exactly one column was ever recorded — the final maximum's (a column is recorded
+      // whenever it raises the maximum) — and nothing was dropped: nothing to filter or sort.
+      int nout = 1;
+      const bool simple = cnt == 1 && !(lostmax >= thr);
+      if (!__all_sync(0xffffffffu, simple || !live)) nout = simple ? 1 : kt_collect(lst, row, cnt, thr, lostmax);
       // a lone survivor equal to the previous label: the point keeps its label, its sums stay where they are
-      const bool need = live && (p.all_to_work || nout != 1 || out[0] != lab);
+      const bool need = live && (p.all_to_work || nout != 1 || lst[row].x != lab);
       const unsigned bal = __ballot_sync(0xffffffffu, need);
       if (bal) {
         unsigned base = 0;
@@ -729,9 +741,12 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         base = __shfl_sync(0xffffffffu, base, 0);
         if (need) {
           int4 *e = reinterpret_cast<int4 *>(p.work + (int64_t)(base + __popc(bal & ((1u << lane) - 1u))) * KT_WORK_INTS);
+          int o[8];
+#pragma unroll
+          for (int s2 = 0; s2 < 8; s2++) o[s2] = s2 < nout ? lst[s2 * KT_ROWS + row].x : -1;
           e[0] = make_int4(gi, nout, 0, 0);
-          e[1] = make_int4(out[0], out[1], out[2], out[3]);
-          e[2] = make_int4(out[4], out[5], out[6], out[7]);
+          e[1] = make_int4(o[0], o[1], o[2], o[3]);
+          e[2] = make_int4(o[4], o[5], o[6], o[7]);
         }
       }
     }
@@ -752,13 +767,50 @@ __device__ __forceinline__ float kt_sum8(float v) {
   return v;
 }
 
-__global__ void __launch_bounds__(256)
+// rare, out of line (keeps the main loop's register count low): the oracle's own arithmetic over the
+// candidates — binary64, dims ascending, separate multiply and add (A1/A2); strict <, lowest index first
+__device__ __noinline__ int kt_exact_rescore(const float *xr, const double *__restrict__ c64, int d, int ncand, bool scan_all,
+                                             int4 cw, int4 cw2) {
+  double best = __longlong_as_double(0x7FF0000000000000LL);
+  int lab = 0;
+  for (int s = 0; s < ncand; s++) {
+    const int j = scan_all ? s : s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : s == 3 ? cw.w : s == 4 ? cw2.x : s == 5 ? cw2.y : s == 6 ? cw2.z : cw2.w;
+    const double dj = km_dist2_f64(xr, c64 + (int64_t)j * d, d);
+    if (dj < best) { best = dj; lab = j; }
+  }
+  return lab;
+}
+
+// a point that changed its label (or every point, in full-update mode) moves between the order-free sums;
+// called by the 8 lanes of its group: consecutive lanes take consecutive dimensions
+__device__ __noinline__ void kt_exact_move(const float *xr, int d, int sl, int lab, int from, long long *__restrict__ acc,
+                                           int64_t sa, int64_t sb, int64_t cnt, double scale_a, double scale_b) {
+  for (int t = sl; t < d; t += 8) {
+    long long a, b;
+    km_fixed_split((double)xr[t], scale_a, scale_b, a, b);
+    km_atomic_add_ll(acc + sa + (int64_t)lab * d + t, a);
+    km_atomic_add_ll(acc + sb + (int64_t)lab * d + t, b);
+    if (from >= 0) {
+      km_atomic_add_ll(acc + sa + (int64_t)from * d + t, -a);
+      km_atomic_add_ll(acc + sb + (int64_t)from * d + t, -b);
+    }
+  }
+  if (sl == 0) {
+    km_atomic_add_ll(acc + cnt + lab, 1);
+    if (from >= 0) km_atomic_add_ll(acc + cnt + from, -1);
+  }
+}
+
+// QN: float4 pieces of a row per lane (d <= 32 * QN).  The loop is a chain of dependent loads (worklist
+// entry -> row of x and previous label -> candidate centroid rows): the next entry is requested one
+// iteration ahead, and the register budget is kept low enough for 3-4 blocks per SM.
+template <int QN>
+__global__ void __launch_bounds__(256, 3)
 km_tensor_exact_kernel(const float *__restrict__ x, int d, int k, const int *__restrict__ work,
                        const unsigned *__restrict__ work_count, const float *__restrict__ chi,
                        const double *__restrict__ c64, int32_t *__restrict__ labels, long long *__restrict__ acc,
                        const KmState *__restrict__ st, int incremental) {
   const KmAccLayout L = km_acc_layout(k, d);
-  const double scale_a = st->scale_a, scale_b = st->scale_b;
   const float tau2 = st->tau_hi;
   const float rho2 = 2.5f * (float)(d + 6) * 0x1.0p-24f;
   const int lane = threadIdx.x & 31, g = lane >> 3, sl = lane & 7;
@@ -766,15 +818,15 @@ km_tensor_exact_kernel(const float *__restrict__ x, int d, int k, const int *__r
   const int64_t nwork = *work_count;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   KmThreadScalars S;
-  // this lane's pieces of a row: float4 index q * 8 + sl, q = 0..3 (d <= 128), zero beyond d
-  auto load_row = [&](const float *row, float4 (&v)[4]) {
+  // this lane's pieces of a row: float4 index q * 8 + sl, q = 0..QN-1, zero beyond d
+  auto load_row = [&](const float *row, float4 (&v)[QN]) {
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
+    for (int q = 0; q < QN; q++) {
       const int e = (q * 8 + sl) * 4;
       v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (e < d) {
         if (vec) {
-          v[q] = *reinterpret_cast<const float4 *>(row + e);
+          v[q] = __ldg(reinterpret_cast<const float4 *>(row + e));
         } else {
           v[q].x = row[e];
           if (e + 1 < d) v[q].y = row[e + 1];
@@ -784,19 +836,25 @@ km_tensor_exact_kernel(const float *__restrict__ x, int d, int k, const int *__r
       }
     }
   };
+  auto load_entry = [&](int64_t w, int4 &hd, int4 &cw, int4 &cw2) {
+    hd = make_int4(0, 0, 0, 0); cw = make_int4(-1, -1, -1, -1); cw2 = cw;
+    if (w < nwork) {
+      const int4 *e = reinterpret_cast<const int4 *>(work + w * KT_WORK_INTS);
+      hd = __ldg(e); cw = __ldg(e + 1); cw2 = __ldg(e + 2);
+    }
+  };
+  int4 hd_n, cw_n, cw2_n;
+  load_entry(warp0 * 4 + g, hd_n, cw_n, cw2_n);
   for (int64_t base = warp0 * 4; base < nwork; base += nwarps * 4) {
     const int64_t w = base + g;
     const bool live = w < nwork;
-    int4 hd = make_int4(0, 0, 0, 0), cw = make_int4(-1, -1, -1, -1), cw2 = make_int4(-1, -1, -1, -1);
-    if (live) {
-      const int4 *e = reinterpret_cast<const int4 *>(work + w * KT_WORK_INTS);
-      hd = e[0]; cw = e[1]; cw2 = e[2];
-    }
+    const int4 hd = hd_n, cw = cw_n, cw2 = cw2_n;
     const int64_t i = hd.x;
     const float *xr = x + (live ? i : 0) * (int64_t)d;
-    float4 xq[4];
+    float4 xq[QN];
     int old = 0;
     if (live) { load_row(xr, xq); old = labels[i]; }
+    load_entry(w + nwarps * 4, hd_n, cw_n, cw2_n);      // the next iteration's entry travels while this one is worked on
     const bool scan_all = hd.y == -2;
     const int ncand = !live ? 0 : scan_all ? k : hd.y;
     auto pick = [&](int s) { return s == 0 ? cw.x : s == 1 ? cw.y : s == 2 ? cw.z : s == 3 ? cw.w : s == 4 ? cw2.x : s == 5 ? cw2.y : s == 6 ? cw2.z : cw2.w; };
@@ -809,10 +867,10 @@ km_tensor_exact_kernel(const float *__restrict__ x, int d, int k, const int *__r
       const int j = scan_all ? s : pick(s);
       float part = 0.f;
       if (act) {
-        float4 cv[4];
+        float4 cv[QN];
         load_row(chi + (int64_t)j * d, cv);
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
+        for (int q = 0; q < QN; q++) {
           float df = xq[q].x - cv[q].x; part = fmaf(df, df, part);
           df = xq[q].y - cv[q].y; part = fmaf(df, df, part);
           df = xq[q].z - cv[q].z; part = fmaf(df, df, part);
@@ -825,37 +883,13 @@ km_tensor_exact_kernel(const float *__restrict__ x, int d, int k, const int *__r
     int lab = i1;
     const bool clear = ncand <= 1 || (b2 - b1) > fmaf(rho2, b2, tau2);
     if (live && !clear && sl == 0) {
-      // binary64, dims ascending, separate multiply and add: the oracle's own arithmetic (A1/A2)
-      double best = __longlong_as_double(0x7FF0000000000000LL);
-      lab = 0;
-      for (int s = 0; s < ncand; s++) {
-        const int j = scan_all ? s : pick(s);
-        const double dj = km_dist2_f64(xr, c64 + (int64_t)j * d, d);
-        if (dj < best) { best = dj; lab = j; }
-      }
+      lab = kt_exact_rescore(xr, c64, d, ncand, scan_all, cw, cw2);
       S.rescored++;
     }
     lab = __shfl_sync(0xffffffffu, lab, g * 8);     // the group's lane 0 holds the decision
     if (live && sl == 0 && lab != old) { S.changed++; labels[i] = lab; }
-    const bool move = live && (incremental ? (lab != old) : true);
-    if (move) {
-      // consecutive lanes take consecutive dimensions: 8 lanes = 64 contiguous bytes per limb row
-      const int from = incremental ? old : -1;
-      for (int t = sl; t < d; t += 8) {
-        long long a, b;
-        km_fixed_split((double)xr[t], scale_a, scale_b, a, b);
-        km_atomic_add_ll(acc + L.sa + (int64_t)lab * d + t, a);
-        km_atomic_add_ll(acc + L.sb + (int64_t)lab * d + t, b);
-        if (from >= 0) {
-          km_atomic_add_ll(acc + L.sa + (int64_t)from * d + t, -a);
-          km_atomic_add_ll(acc + L.sb + (int64_t)from * d + t, -b);
-        }
-      }
-      if (sl == 0) {
-        km_atomic_add_ll(acc + L.cnt + lab, 1);
-        if (from >= 0) km_atomic_add_ll(acc + L.cnt + from, -1);
-      }
-    }
+    if (live && (incremental ? (lab != old) : true))
+      kt_exact_move(xr, d, sl, lab, incremental ? old : -1, acc, L.sa, L.sb, L.cnt, st->scale_a, st->scale_b);
   }
   km_flush_scalars(S, acc, L);
 }
@@ -951,8 +985,14 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   // ---- exact stage over the worklist (its length is read on the device)
   const int64_t want = (a.n * 8 + 255) / 256;
   const int64_t cap2 = (int64_t)a.sm_count * 8;
-  km_tensor_exact_kernel<<<(int)(want < cap2 ? want : cap2), 256, 0, a.stream>>>(
-      (const float *)a.x, a.d, a.k, a.t_work, a.t_work_count, a.chi, a.c64, a.labels, a.acc, a.state, a.incremental);
+  const int eg = (int)(want < cap2 ? want : cap2);
+#define KT_EXACT(QN)                                                                                                  \
+  km_tensor_exact_kernel<QN><<<eg, 256, 0, a.stream>>>((const float *)a.x, a.d, a.k, a.t_work, a.t_work_count, a.chi, \
+                                                       a.c64, a.labels, a.acc, a.state, a.incremental)
+  if (a.d <= 32) KT_EXACT(1);
+  else if (a.d <= 64) KT_EXACT(2);
+  else KT_EXACT(4);
+#undef KT_EXACT
   (*launches)++;
   return cudaGetLastError();
 }
