@@ -438,6 +438,16 @@ def measure(job, key, wl, steps, warmup, burn_s, keep_state=False):
                   "centroid_sha": hashlib.sha256(np.ascontiguousarray(c_used).tobytes()).hexdigest()[:16]}
     del lab
 
+    # the whole-job call on the resident points: km_run(R) from the same start (device time of the call)
+    st.set_centroids(c0)
+    l0 = st.launch_count()
+    rs = st.run(20)
+    run_launches = st.launch_count() - l0
+    run_ms = job.max_over_ranks(rs["device_ms"])
+    run_info = {"iterations": rs["iterations"], "ms_per_iteration": run_ms / max(1, rs["iterations"]), "launches": run_launches,
+                "how": "one cooperative launch, points resident in shared memory" if run_launches <= 2 and rs["iterations"] > 2
+                       else "one launch sequence per iteration"}
+
     res = {
         "workload": wl["name"], "n_total": n_total, "n_per_gpu": n, "d": d, "k": k, "scaling": scaling,
         "value": n_total * steps / (total_ms * 1e-3), "ms_per_step": total_ms / steps, "steps": steps,
@@ -446,6 +456,7 @@ def measure(job, key, wl, steps, warmup, burn_s, keep_state=False):
         "changed_at_last_step": last["changed"], "parity_check": parity,
         "step_ms_min_med_max": [min(step_ms), statistics.median(step_ms), max(step_ms)],
         "step_ms": [round(v, 4) for v in step_ms],
+        "km_run": run_info,
         "collective": "none (one rank)" if world == 1 else
                       ("one-shot kernel over peer memory" if st.comm_info()[2] == 2 else "ncclAllReduce(int64)"),
     }

@@ -448,6 +448,7 @@ extern "C" km_status km_create(const km_config *cfg, km_ctx **out) {
   KM_CREATE_CUDA(cudaSetDevice(ctx->device));
   KM_CREATE_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device));
   KM_CREATE_CUDA(cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+  KM_CREATE_CUDA(cudaDeviceGetAttribute(&ctx->coop_ok, cudaDevAttrCooperativeLaunch, ctx->device));
   if (c.stream) {
     ctx->stream = (cudaStream_t)c.stream;
   } else {
@@ -1301,6 +1302,44 @@ extern "C" km_status km_reset_labels(km_ctx *ctx) {
   return KM_OK;
 }
 
+// km_run of a job that fits in shared memory (km_resident.cu): the whole loop in one cooperative launch.
+// Entered after reset_labels: labels -1, sums and delta tables zero, no pass pending.
+static km_status run_resident(km_ctx *ctx, int32_t max_iter, km_stats *stats, int per_block, int grid, size_t smem) {
+  KmResidentArgs a;
+  a.x = (const float *)ctx->x; a.labels = ctx->labels; a.n = ctx->n; a.d = ctx->d; a.k = ctx->k;
+  a.per_block = per_block; a.grid = grid; a.smem = smem; a.max_iter = max_iter;
+  a.C_in = ctx->p1C[ctx->p1_s]; a.C_out = ctx->p1C[ctx->p1_s]; a.S_out = ctx->p1S[ctx->p1_s];
+  for (int q = 0; q < 3; q++) a.Dt[q] = ctx->p1D[q];
+  a.ring = ctx->ring_dev; a.state_it = &ctx->state->it;
+  a.scale_a = ldexp(1.0, ctx->qa); a.scale_b = ldexp(1.0, ctx->QB); a.QB = ctx->QB; a.qa = ctx->qa;
+  a.Ta = ctx->Ta; a.Tb = ctx->Tb; a.qt = ctx->qt; a.QBt = ctx->QBt;
+  inertia_grid(ctx, &a.qg, &a.QBg);
+  {
+    KmAssignArgs f;   // the filter's error terms, from the same host-side bound as the stepwise kernels'
+    fill_assign_args(ctx, f);
+    a.tau2 = f.h_tau_hi;
+    a.rho2 = 2.5f * (float)(ctx->d + 6) * 0x1.0p-24f;
+  }
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  KM_CUDA(ctx, km_launch_resident(a, ctx->stream, &ctx->launches));   // leaves the three delta tables empty again
+  KM_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  KM_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+  const KmStatSlot last = ctx->ring[0];
+  if (last.it < 1 || last.it > max_iter) return fail(ctx, KM_ERR_STATE, "resident run: no result");
+  ctx->host_it = (int32_t)last.it;
+  ctx->p1_pend_it = ctx->host_it;
+  ctx->p1_pending = false;
+  ctx->p1_dw = 0;
+  ctx->labels_fresh = false;
+  ctx->last_path = KM_PATH_FILTER_F32;
+  ctx->passes_since_upload += ctx->host_it;
+  ctx->ring[ctx->host_it % KM_RING] = last;
+  fill_stats(ctx, last, stats, ms);
+  return KM_OK;
+}
+
 // A5.  The device decides by itself whether an iteration's update happens (changed > 0),
 // so the host may keep KM_RUN_LAG iterations in flight: passes issued after convergence
 // change nothing, and the first slot with changed == 0 is the answer.
@@ -1310,6 +1349,12 @@ extern "C" km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats) {
   if (s != KM_OK) return s;
   if (max_iter < 1) return fail(ctx, KM_ERR_INVALID_ARG, "km_run: max_iter must be >= 1");
   if ((s = reset_labels(ctx)) != KM_OK) return s;
+  if (ctx->p1 && ctx->world == 1 && ctx->coop_ok && ctx->cfg.update_mode == KM_UPDATE_INCREMENTAL && !ctx->cfg.profile_kernels) {
+    int per_block = 0, grid = 0;
+    size_t smem = 0;
+    if (km_resident_plan(ctx->n, ctx->d, ctx->k, ctx->dtype, ctx->sm_count, ctx->max_smem_optin, &per_block, &grid, &smem))
+      return run_resident(ctx, max_iter, stats, per_block, grid, smem);
+  }
   if (max_iter >= 3 && ctx->passes_since_upload < 2) ctx->passes_since_upload = 2;  // an iterating job: lay the store out for it now
   if ((s = maybe_sort_points(ctx)) != KM_OK) return s;
   KM_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));

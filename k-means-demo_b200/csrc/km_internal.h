@@ -64,6 +64,7 @@ struct km_ctx {
   cudaEvent_t ring_ev[KM_RING];
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int64_t launches = 0;
+  int coop_ok = 0;                  // device supports cooperative launches (km_resident.cu)
   int32_t host_it = 0;              // assign steps issued since the last label reset
   int32_t last_path = 0;
   int32_t QB = 0, qa = 0, E = 0, NB = 0;
@@ -169,6 +170,17 @@ bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_poi
                           int fine, KmPrune2 *out);
 cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, int64_t len,
                                      unsigned long long epoch, long long *out, int *err, cudaStream_t s, int64_t *launches);
+// km_resident.cu: the whole km_run loop in one cooperative launch for jobs that fit in shared memory
+#define KM_RESIDENT_MAX_KD 32    // binary64 argmin over all k, no filter: only worth it while k * d is small
+struct KmResidentArgs {
+  const float *x; int32_t *labels; int64_t n; int d, k, per_block, grid, max_iter; size_t smem;
+  const double *C_in; double *C_out; long long *S_out; long long *Dt[3];
+  KmStatSlot *ring; int32_t *state_it;
+  double scale_a, scale_b; float tau2, rho2; int QB, qa; long long Ta, Tb; int qt, QBt, qg, QBg;
+};
+bool km_resident_plan(int64_t n, int32_t d, int32_t k, int dtype, int sm_count, int max_smem_optin, int *per_block, int *grid,
+                      size_t *smem);
+cudaError_t km_launch_resident(const KmResidentArgs &a, cudaStream_t stream, int64_t *launches);
 #define KM_PRUNE_MAX_GP 260   // finest grid side (256 cells + margins)
 bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin);
 
