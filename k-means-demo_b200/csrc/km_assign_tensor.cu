@@ -411,6 +411,71 @@ __device__ __noinline__ int kt_collect(int2 *lst, int row, int cnt, float thr, f
   return w;
 }
 
+// The producers' loop with the row geometry fixed at compile time (RPP rows per warp sweep, 32 / RPP lanes
+// per row; d a multiple of 4; an index list present).  Same work as the generic loop in the kernel, a
+// quarter of its instructions: row numbers, bounds and index offsets are constants after unrolling.  The
+// producers are the pacing role of the coarse stage at d = 128 (six warps, always busy, ~60 instructions
+// per row in the generic loop), so this is where the cycles are.
+template <int RPP>
+__device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsigned *__restrict__ porder, int64_t pn, int d, unsigned char *smem_raw, uint32_t tile_bytes, int astages,
+                                        uint64_t *a_full, uint64_t *a_empty, int64_t passes, int pw, int lane) {
+  constexpr int LPR = 32 / RPP;                     // lanes per row
+  constexpr int RSTEP = KT_PROD_WARPS * RPP;       // rows between two sweeps of one warp
+  constexpr int BATCH = 16;                         // loads in flight per lane
+  constexpr int NB = (KT_ROWS + BATCH * RSTEP - 1) / (BATCH * RSTEP);   // batches per pass
+  const int c4 = d >> 2;
+  const int r_off = lane / LPR, q = lane % LPR;
+  const bool active = q < c4;
+  const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
+  const int rbase = pw * RPP + r_off;               // this lane's first row of every pass
+  const uint32_t lane_off = (uint32_t)(kb * KT_KB_BYTES + within);
+  const float *xe = px + e;
+  int gi[BATCH];
+  // indices of batch b (a compile-time number after unrolling) of pass ps
+#define KT_FETCH(PS, B)                                                                                        \
+  {                                                                                                            \
+    const int64_t row0_ = (PS) * KT_ROWS;                                                                      \
+    const int nrows_ = (int)min((int64_t)KT_ROWS, pn - row0_);                                                 \
+    const unsigned *o_ = porder + row0_ + rbase;                                                               \
+    _Pragma("unroll") for (int u = 0; u < BATCH; u++) {                                                        \
+      const int r_ = rbase + ((B) * BATCH + u) * RSTEP;                                                        \
+      gi[u] = (active && r_ < nrows_) ? (int)__ldg(o_ + ((B) * BATCH + u) * RSTEP) : -1;                       \
+    }                                                                                                          \
+  }
+  int it = 0;
+  if ((int64_t)blockIdx.x < passes) KT_FETCH((int64_t)blockIdx.x, 0)
+  for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
+    const int s = it % astages;
+    mbar_wait_relaxed(&a_empty[s], ((it / astages) & 1) ^ 1);
+    unsigned char *stage = smem_raw + (size_t)s * 2 * tile_bytes + lane_off;
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+      float4 v[BATCH];
+#pragma unroll
+      for (int u = 0; u < BATCH; u++) {
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gi[u] >= 0) v[u] = ldg_stream4(xe + (int64_t)gi[u] * d);   // read once: keep it out of L1
+      }
+      // the next batch's indices (this pass's, or the first of the next pass) fly under these loads
+      if (b + 1 < NB) KT_FETCH(ps, b + 1)
+      else if (ps + gridDim.x < passes) KT_FETCH(ps + gridDim.x, 0)
+#pragma unroll
+      for (int u = 0; u < BATCH; u++) {
+        const int r = rbase + (b * BATCH + u) * RSTEP;
+        if (active && r < KT_ROWS) {
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
+          const int rr = r & (KT_M - 1);
+          unsigned char *dst = stage + (r >> 7) * tile_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4);
+          *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
+        }
+      }
+    }
+    fence_proxy_async();
+    mbar_arrive(&a_full[s]);
+  }
+#undef KT_FETCH
+}
+
 // HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
 // would wait in line behind the producers' stream of point loads)
 template <bool HSMEM, bool FOLD>
@@ -489,6 +554,12 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
     const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
     const int rstep = KT_PROD_WARPS * rpp;
     const bool vec = (d & 3) == 0;
+    if (vec && p.order != nullptr && (rpp == 1 || rpp == 2 || rpp == 4)) {
+      // the common row widths (d = 128, 64, 32 and everything that sweeps like them): compile-time geometry
+      if (rpp == 1) kt_produce<1>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
+      else if (rpp == 2) kt_produce<2>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
+      else kt_produce<4>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
+    } else {
     constexpr int BATCH = 16;
     // row indices of one batch: position -> row of x through the label-ordered list
     auto fetch_idx = [&](int64_t row0, int rb, int (&gi)[BATCH]) {
@@ -541,6 +612,7 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
       }
       fence_proxy_async();
       mbar_arrive(&a_full[s]);
+    }
     }
   } else if (warp == KT_WARP_TMA) {
     // ===================== TMA: centroid tiles (the whole warp walks the loop, one elected lane issues) =====================
