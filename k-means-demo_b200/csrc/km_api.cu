@@ -1079,8 +1079,11 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
     a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_hist = ctx->t_hist; a.t_work_count = ctx->t_work_count;
     a.t_order = ctx->t_order; a.t_work = ctx->t_work;
     a.t_labels_fresh = ctx->labels_fresh ? 1 : 0;
-    // the first passes re-label many points: rebuild the list every time; later every fourth pass
-    a.t_order_reuse = (ctx->t_order_valid && ctx->host_it >= 6 && ctx->t_order_age < 3) ? 1 : 0;
+    // the first passes re-label many points: rebuild the list every time; later the list ages gracefully
+    // (a fraction of a percent of the labels change per pass), so the interval grows with the iteration
+    // count: every fourth pass at first, every 16th at most
+    const int max_age = std::min(16, std::max(3, ctx->host_it / 2));
+    a.t_order_reuse = (ctx->t_order_valid && ctx->host_it >= 6 && ctx->t_order_age < max_age) ? 1 : 0;
     if (!a.t_labels_fresh) {
       if (a.t_order_reuse) ctx->t_order_age++;
       else { ctx->t_order_valid = true; ctx->t_order_age = 0; }

@@ -429,9 +429,12 @@ __device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsi
   const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
   const int rbase = pw * RPP + r_off;               // this lane's first row of every pass
   const uint32_t lane_off = (uint32_t)(kb * KT_KB_BYTES + within);
-  const float *xe = px + e;
-  int gi[BATCH];
-  // indices of batch b (a compile-time number after unrolling) of pass ps
+  const unsigned char *xeb = reinterpret_cast<const unsigned char *>(px + e);   // this lane's 16-byte piece of row 0
+  const unsigned row_bytes = (unsigned)d * 4u;
+  unsigned gi[BATCH];
+  // Row numbers of batch b (a compile-time number after unrolling) of pass ps.  A slot past the end of the
+  // shard reads row 0 instead: its tile row then holds finite junk that no epilogue lane looks at (their
+  // own look-up marks the row as dead), and the loop needs neither a predicate nor a zero fill per load.
 #define KT_FETCH(PS, B)                                                                                        \
   {                                                                                                            \
     const int64_t row0_ = (PS) * KT_ROWS;                                                                      \
@@ -439,7 +442,8 @@ __device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsi
     const unsigned *o_ = porder + row0_ + rbase;                                                               \
     _Pragma("unroll") for (int u = 0; u < BATCH; u++) {                                                        \
       const int r_ = rbase + ((B) * BATCH + u) * RSTEP;                                                        \
-      gi[u] = (active && r_ < nrows_) ? (int)__ldg(o_ + ((B) * BATCH + u) * RSTEP) : -1;                       \
+      gi[u] = 0;                                                                                               \
+      if (r_ < nrows_) gi[u] = __ldg(o_ + ((B) * BATCH + u) * RSTEP);                                          \
     }                                                                                                          \
   }
   int it = 0;
@@ -451,10 +455,11 @@ __device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsi
 #pragma unroll
     for (int b = 0; b < NB; b++) {
       float4 v[BATCH];
+      if (active) {
 #pragma unroll
-      for (int u = 0; u < BATCH; u++) {
-        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gi[u] >= 0) v[u] = ldg_stream4(xe + (int64_t)gi[u] * d);   // read once: keep it out of L1
+        for (int u = 0; u < BATCH; u++)
+          if ((b * BATCH + u) * RSTEP < KT_ROWS)       // compile time: slots that can hold a row of the pass at all
+            v[u] = ldg_stream4(reinterpret_cast<const float *>(xeb + (uint64_t)gi[u] * row_bytes));   // one IMAD.WIDE.U32; read once: keep it out of L1
       }
       // the next batch's indices (this pass's, or the first of the next pass) fly under these loads
       if (b + 1 < NB) KT_FETCH(ps, b + 1)
@@ -462,7 +467,7 @@ __device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsi
 #pragma unroll
       for (int u = 0; u < BATCH; u++) {
         const int r = rbase + (b * BATCH + u) * RSTEP;
-        if (active && r < KT_ROWS) {
+        if ((b * BATCH + u) * RSTEP < KT_ROWS && active && r < KT_ROWS) {
           const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
           const int rr = r & (KT_M - 1);
           unsigned char *dst = stage + (r >> 7) * tile_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4);
