@@ -100,6 +100,8 @@ static void free_points(km_ctx *ctx) {
   if (ctx->t_work) cudaFree(ctx->t_work);
   if (ctx->t_order) cudaFree(ctx->t_order);
   if (ctx->t_xn) cudaFree(ctx->t_xn);
+  if (ctx->t_xbf) cudaFree(ctx->t_xbf);
+  ctx->t_xbf = nullptr; ctx->t_xbf_bytes = 0;
   ctx->t_work = nullptr; ctx->t_order = nullptr; ctx->t_xn = nullptr; ctx->t_work_n = 0; ctx->t_xn_valid = false;
   ctx->x = nullptr; ctx->labels = nullptr; ctx->own_x = false; ctx->have_points = false;
   ctx->n = 0; ctx->n_total = 0; ctx->i0 = 0;
@@ -1013,7 +1015,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   memset(&a.ps, 0, sizeof(a.ps));
   memset(&a.pr, 0, sizeof(a.pr));
   a.t_cn = nullptr; a.t_cbf = nullptr; a.t_hist = nullptr; a.t_work_count = nullptr; a.t_order = nullptr; a.t_work = nullptr;
-  a.t_labels_fresh = 0; a.t_order_reuse = 0; a.t_xnmax = 0.f; a.t_xn = nullptr;
+  a.t_labels_fresh = 0; a.t_order_reuse = 0; a.t_xnmax = 0.f; a.t_xn = nullptr; a.t_xbf = nullptr;
   a.prune = 0;
   if (ctx->have_bbox && ctx->cfg.no_prune == 0 &&
       km_small_prune_setup(ctx->d, ctx->k, ctx->n, ctx->cfg.prune_min_points, ctx->sm_count, ctx->bbox, ctx->perm ? 1 : 0, &a.pr))
@@ -1071,11 +1073,20 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
       ctx->t_xn_valid = false;
       ctx->t_order_valid = false;
     }
-    if (!ctx->t_xn_valid) {   // once per upload
+    if (ctx->t_xbf_bytes < km_tensor_xbf_bytes(ctx->n, ctx->d)) {
+      if (ctx->t_xbf) cudaFree(ctx->t_xbf);
+      ctx->t_xbf = nullptr; ctx->t_xbf_bytes = 0;
+      KM_CUDA(ctx, cudaMalloc(&ctx->t_xbf, km_tensor_xbf_bytes(ctx->n, ctx->d)));
+      ctx->t_xbf_bytes = km_tensor_xbf_bytes(ctx->n, ctx->d);
+      ctx->t_xn_valid = false;
+    }
+    if (!ctx->t_xn_valid) {   // once per upload: the rows' norms and their BF16 copy
       KM_CUDA(ctx, km_launch_row_norms((const float *)ctx->x, ctx->n, ctx->d, ctx->t_xn, ctx->sm_count, ctx->stream, &ctx->launches));
+      KM_CUDA(ctx, km_launch_xbf((const float *)ctx->x, ctx->n, ctx->d, ctx->t_xbf, ctx->sm_count, ctx->stream, &ctx->launches));
       ctx->t_xn_valid = true;
     }
     a.t_xn = ctx->t_xn;
+    a.t_xbf = ctx->t_xbf;
     a.t_cn = ctx->t_cn; a.t_cbf = ctx->t_cbf; a.t_hist = ctx->t_hist; a.t_work_count = ctx->t_work_count;
     a.t_order = ctx->t_order; a.t_work = ctx->t_work;
     a.t_labels_fresh = ctx->labels_fresh ? 1 : 0;

@@ -9,9 +9,12 @@
 //           cluster then sit in the same warps of the coarse stage, so a warp's 32 points find
 //           their few candidate centroids in the same columns (points never move; only an index
 //           list is rebuilt, and every per-cluster sum is order-free).
+//  xbf      once per upload: a BF16 copy of x (rows zero-padded to 64-column blocks, plus the 1.0 columns
+//           of the folded h), so that the coarse stage can take its point rows by TMA.
 //  coarse   km_tensor_coarse_kernel, warp-specialised, one CTA per SM, 256 points per pass:
-//             6 producer warps  gather the pass's rows of x by the index list, convert to BF16 and
-//                               store them K-major / SWIZZLE_128B (two 128-row tiles, 2-4 stages);
+//             4 gather warps    cp.async.bulk.tensor ... tile::gather4: the pass's rows of the BF16 copy, picked
+//                               by the index list, land K-major / SWIZZLE_128B in two 128-row tiles (2-4
+//                               stages, mbarrier complete_tx) — no thread loads, converts or stores a point;
 //             1 TMA warp        an elected lane streams 128-centroid tiles of the BF16 copy with
 //                               cp.async.bulk.tensor (2-4 stages, mbarrier complete_tx), starting
 //                               with the tile that holds the pass's previous label;
@@ -45,10 +48,11 @@
 #define KT_ROWS 256         // points per CTA pass: two MMA tiles
 #define KT_LIST 8           // per-point survivor list kept in shared memory while the tiles stream by
 #define KT_EPI_WARPS 8      // warp w: point tile w >> 2, TMEM lane quadrant w & 3
-#define KT_PROD_WARPS 6
-#define KT_WARP_MMA (KT_EPI_WARPS + KT_PROD_WARPS)
-#define KT_WARP_TMA (KT_WARP_MMA + 1)
-#define KT_THREADS ((KT_WARP_TMA + 1) * 32)   // 512
+#define KT_WARP_GATHER KT_EPI_WARPS          // TMA: rows of the BF16 copy of x, gathered by the index list ...
+#define KT_GATHER_WARPS 4                    // ... by four warps, 16 lanes of each (a TMA instruction is issued lane by lane: more warps, more issue)
+#define KT_WARP_MMA (KT_EPI_WARPS + KT_GATHER_WARPS)
+#define KT_WARP_TMA (KT_WARP_MMA + 1)        // TMA: centroid tiles
+#define KT_THREADS ((KT_WARP_TMA + 1) * 32)   // 448
 #define KT_KB_BYTES (KT_M * 128)   // one 64-element (128-byte) k-block of a 128-row tile: 16 KiB
 #define KT_WORK_INTS 12     // worklist entry: {row, n (or -2: scan all k), 0, 0, c0..c7}
 
@@ -94,6 +98,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_dst),
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// TMA gather: four rows of the 2-D tensor map, picked by their row numbers, one box-width of columns each
+// -> four consecutive 128-byte rows in shared memory (swizzled by the hardware like any other tile)
+__device__ __forceinline__ void tma_gather4(uint32_t smem_dst, const CUtensorMap *map, int c0, int r0, int r1, int r2, int r3, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(smem_dst),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
       : "memory");
 }
 
@@ -247,6 +260,42 @@ cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn,
   if (n == 0) return cudaSuccess;
   const int64_t want = (n * 8 + 255) / 256, cap = (int64_t)sm_count * 16;
   km_row_norm_kernel<<<(int)(want < cap ? want : cap), 256, 0, s>>>(x, n, d, xn);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ BF16 copy of x, once per upload
+// Row i: the d coordinates rounded to BF16 (round to nearest even — the rounding the error window of the
+// coarse stage assumes), zero up to the padded width drow = 64 * kblocks, and — when h rides in the
+// contraction (kt_fold) — 1.0 in the three columns that multiply the split h.  The coarse stage gathers
+// these rows by TMA straight into its operand tiles: half the bytes of the binary32 rows, no conversion
+// in the kernel.  Eight elements (16 bytes) per thread.
+__global__ void __launch_bounds__(256) km_tensor_xbf_kernel(const float *__restrict__ x, int64_t n, int d, int drow, int fold_col,
+                                                            __nv_bfloat16 *__restrict__ xbf) {
+  const int per_row = drow >> 3;
+  const int64_t total = n * per_row;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = w / per_row;
+    const int c0 = (int)(w - i * per_row) * 8;
+    __align__(16) __nv_bfloat16 o[8];
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+      const int c = c0 + t;
+      float v = c < d ? x[i * d + c] : 0.f;
+      if (fold_col >= 0 && c >= fold_col && c < fold_col + 3) v = 1.f;
+      o[t] = __float2bfloat16_rn(v);
+    }
+    *reinterpret_cast<uint4 *>(xbf + i * drow + c0) = *reinterpret_cast<const uint4 *>(o);
+  }
+}
+
+size_t km_tensor_xbf_bytes(int64_t n, int32_t d) { return (size_t)(n > 0 ? n : 1) * kt_kblocks(d) * 64 * sizeof(__nv_bfloat16); }
+cudaError_t km_launch_xbf(const float *x, int64_t n, int32_t d, void *xbf, int sm_count, cudaStream_t s, int64_t *launches) {
+  if (n == 0) return cudaSuccess;
+  const int drow = kt_kblocks(d) * 64;
+  const int64_t want = (n * (drow / 8) + 255) / 256, cap = (int64_t)sm_count * 16;
+  km_tensor_xbf_kernel<<<(int)(want < cap ? want : cap), 256, 0, s>>>(x, n, d, drow, kt_fold(d) ? ((d + 15) & ~15) : -1,
+                                                                       (__nv_bfloat16 *)xbf);
   (*launches)++;
   return cudaGetLastError();
 }
@@ -411,80 +460,10 @@ __device__ __noinline__ int kt_collect(int2 *lst, int row, int cnt, float thr, f
   return w;
 }
 
-// The producers' loop with the row geometry fixed at compile time (RPP rows per warp sweep, 32 / RPP lanes
-// per row; d a multiple of 4; an index list present).  Same work as the generic loop in the kernel, a
-// quarter of its instructions: row numbers, bounds and index offsets are constants after unrolling.  The
-// producers are the pacing role of the coarse stage at d = 128 (six warps, always busy, ~60 instructions
-// per row in the generic loop), so this is where the cycles are.
-template <int RPP>
-__device__ __noinline__ void kt_produce(const float *__restrict__ px, const unsigned *__restrict__ porder, int64_t pn, int d, unsigned char *smem_raw, uint32_t tile_bytes, int astages,
-                                        uint64_t *a_full, uint64_t *a_empty, int64_t passes, int pw, int lane) {
-  constexpr int LPR = 32 / RPP;                     // lanes per row
-  constexpr int RSTEP = KT_PROD_WARPS * RPP;       // rows between two sweeps of one warp
-  constexpr int BATCH = 16;                         // loads in flight per lane
-  constexpr int NB = (KT_ROWS + BATCH * RSTEP - 1) / (BATCH * RSTEP);   // batches per pass
-  const int c4 = d >> 2;
-  const int r_off = lane / LPR, q = lane % LPR;
-  const bool active = q < c4;
-  const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
-  const int rbase = pw * RPP + r_off;               // this lane's first row of every pass
-  const uint32_t lane_off = (uint32_t)(kb * KT_KB_BYTES + within);
-  const unsigned char *xeb = reinterpret_cast<const unsigned char *>(px + e);   // this lane's 16-byte piece of row 0
-  const unsigned row_bytes = (unsigned)d * 4u;
-  unsigned gi[BATCH];
-  // Row numbers of batch b (a compile-time number after unrolling) of pass ps.  A slot past the end of the
-  // shard reads row 0 instead: its tile row then holds finite junk that no epilogue lane looks at (their
-  // own look-up marks the row as dead), and the loop needs neither a predicate nor a zero fill per load.
-#define KT_FETCH(PS, B)                                                                                        \
-  {                                                                                                            \
-    const int64_t row0_ = (PS) * KT_ROWS;                                                                      \
-    const int nrows_ = (int)min((int64_t)KT_ROWS, pn - row0_);                                                 \
-    const unsigned *o_ = porder + row0_ + rbase;                                                               \
-    _Pragma("unroll") for (int u = 0; u < BATCH; u++) {                                                        \
-      const int r_ = rbase + ((B) * BATCH + u) * RSTEP;                                                        \
-      gi[u] = 0;                                                                                               \
-      if (r_ < nrows_) gi[u] = __ldg(o_ + ((B) * BATCH + u) * RSTEP);                                          \
-    }                                                                                                          \
-  }
-  int it = 0;
-  if ((int64_t)blockIdx.x < passes) KT_FETCH((int64_t)blockIdx.x, 0)
-  for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
-    const int s = it % astages;
-    mbar_wait_relaxed(&a_empty[s], ((it / astages) & 1) ^ 1);
-    unsigned char *stage = smem_raw + (size_t)s * 2 * tile_bytes + lane_off;
-#pragma unroll
-    for (int b = 0; b < NB; b++) {
-      float4 v[BATCH];
-      if (active) {
-#pragma unroll
-        for (int u = 0; u < BATCH; u++)
-          if ((b * BATCH + u) * RSTEP < KT_ROWS)       // compile time: slots that can hold a row of the pass at all
-            v[u] = ldg_stream4(reinterpret_cast<const float *>(xeb + (uint64_t)gi[u] * row_bytes));   // one IMAD.WIDE.U32; read once: keep it out of L1
-      }
-      // the next batch's indices (this pass's, or the first of the next pass) fly under these loads
-      if (b + 1 < NB) KT_FETCH(ps, b + 1)
-      else if (ps + gridDim.x < passes) KT_FETCH(ps + gridDim.x, 0)
-#pragma unroll
-      for (int u = 0; u < BATCH; u++) {
-        const int r = rbase + (b * BATCH + u) * RSTEP;
-        if ((b * BATCH + u) * RSTEP < KT_ROWS && active && r < KT_ROWS) {
-          const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
-          const int rr = r & (KT_M - 1);
-          unsigned char *dst = stage + (r >> 7) * tile_bytes + rr * 128 + ((ch ^ (rr & 7)) << 4);
-          *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
-        }
-      }
-    }
-    fence_proxy_async();
-    mbar_arrive(&a_full[s]);
-  }
-#undef KT_FETCH
-}
-
 // HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
 // would wait in line behind the producers' stream of point loads)
 template <bool HSMEM, bool FOLD>
-__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmB, const KtParams p) {
+__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const KtParams p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const int d = p.d, kblocks = kt_kblocks(d), bstages = kt_bstages(d);
   const int nks = ((d + 15) >> 4) + (FOLD ? 1 : 0);             // K = 16 MMA steps over the (zero-padded) dimension [+ the h columns]
@@ -505,22 +484,10 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   const uint32_t hs_addr = smem_u32(hs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // the operand region starts as zeros: the padding columns (d .. kblocks*64) are never written again
-  for (uint32_t o = threadIdx.x * 16; o < (uint32_t)astages * 2 * tile_bytes; o += KT_THREADS * 16)
-    *reinterpret_cast<uint4 *>(smem_raw + o) = make_uint4(0, 0, 0, 0);
-  if (FOLD) {
-    // ... except the three columns that multiply the split h: 1.0 in every row of every stage
-    __syncthreads();
-    const int fc = ((d + 15) & ~15), fkb = fc >> 6, feb = fc & 63, fch = feb >> 3, fwithin = (feb & 7) * 2;
-    for (int r = threadIdx.x; r < astages * 2 * KT_M; r += KT_THREADS) {
-      const int rr = r & (KT_M - 1);
-      unsigned char *dst = smem_raw + (size_t)(r >> 7) * tile_bytes + fkb * KT_KB_BYTES + rr * 128 + ((fch ^ (rr & 7)) << 4) + fwithin;
-      *reinterpret_cast<uint2 *>(dst) = make_uint2(0x3F803F80u, 0x00003F80u);   // bf16 {1, 1, 1, 0}
-    }
-  }
+  // (the point tiles arrive whole by TMA from the BF16 copy of x: zero padding and — FOLD — the 1.0 columns are part of its rows)
   fence_proxy_async();
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 4; s++) { mbar_init(&a_full[s], KT_PROD_WARPS * 32); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < 4; s++) { mbar_init(&a_full[s], KT_GATHER_WARPS); mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < 4; s++) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
     for (int s = 0; s < 2; s++) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], KT_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -549,75 +516,43 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   auto start_of = [&](int gi0) -> int { return gi0 < 0 ? 0 : __ldg(p.labels + gi0); };
   auto start_ok = [&](int lab) -> int { return (lab >= 0 && lab < p.k) ? lab : 0; };
 
-  if (warp >= KT_EPI_WARPS && warp < KT_WARP_MMA) {
-    // ===================== producers: rows of x -> BF16, K-major, swizzled =====================
-    const int pw = warp - KT_EPI_WARPS;
-    const int c4 = (d + 3) >> 2;                  // 16-byte pieces of a row (the last may be partial)
-    const int rpp = 32 / c4;                      // rows per warp sweep
-    const int r_off = lane / c4, q = lane - r_off * c4;
-    const bool active = r_off < rpp;
-    const int e = q * 4, kb = e >> 6, eb = e & 63, ch = eb >> 3, within = (eb & 7) * 2;
-    const int rstep = KT_PROD_WARPS * rpp;
-    const bool vec = (d & 3) == 0;
-    if (vec && p.order != nullptr && (rpp == 1 || rpp == 2 || rpp == 4)) {
-      // the common row widths (d = 128, 64, 32 and everything that sweeps like them): compile-time geometry
-      if (rpp == 1) kt_produce<1>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
-      else if (rpp == 2) kt_produce<2>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
-      else kt_produce<4>(p.x, p.order, p.n, d, smem_raw, tile_bytes, astages, a_full, a_empty, passes, pw, lane);
-    } else {
-    constexpr int BATCH = 16;
-    // row indices of one batch: position -> row of x through the label-ordered list
-    auto fetch_idx = [&](int64_t row0, int rb, int (&gi)[BATCH]) {
+  if (warp >= KT_WARP_GATHER && warp < KT_WARP_MMA) {
+    // ===================== TMA: the pass's 256 rows of the BF16 copy of x, gathered through the index list =====================
+    // 64 lanes (16 of each gather warp) own four consecutive rows of the pass each: a lane reads their row
+    // numbers (16 contiguous bytes of the list, one pass ahead) and issues one tile::gather4 per 64-column block.
+    // The rows land in the K-major SWIZZLE_128B layout the MMA reads; nothing is converted or stored by any thread.
+    constexpr int GL = 64 / KT_GATHER_WARPS;                        // issuing lanes per gather warp
+    const bool on = lane < GL;
+    const int gl = (warp - KT_WARP_GATHER) * GL + (on ? lane : 0);  // 0 .. 63: rows 4 gl .. 4 gl + 3
+    auto rows_of = [&](int64_t ps, int (&idx)[4]) {
+      const int64_t r0 = ps * KT_ROWS + gl * 4;
 #pragma unroll
-      for (int u = 0; u < BATCH; u++) {
-        const int r = rb + u * rstep;
-        gi[u] = -1;
-        if (active && r < KT_ROWS && row0 + r < p.n) gi[u] = p.order ? (int)__ldg(p.order + row0 + r) : (int)(row0 + r);
+      for (int i = 0; i < 4; i++) idx[i] = (int)min(p.n, r0 + i);            // past the end: row n, out of bounds -> zero fill
+      if (ps < passes && p.order != nullptr) {
+        if (r0 + 4 <= p.n) {
+          const uint4 a4 = __ldg(reinterpret_cast<const uint4 *>(p.order + r0));
+          idx[0] = (int)a4.x; idx[1] = (int)a4.y; idx[2] = (int)a4.z; idx[3] = (int)a4.w;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+            if (r0 + i < p.n) idx[i] = (int)__ldg(p.order + r0 + i);
+        }
       }
     };
     int it = 0;
-    int gi[BATCH];
-    if ((int64_t)blockIdx.x < passes) fetch_idx((int64_t)blockIdx.x * KT_ROWS, pw * rpp + r_off, gi);
+    int idx[4];
+    rows_of(blockIdx.x, idx);
+    const uint32_t lane_dst = (uint32_t)((gl >> 5) * tile_bytes + (gl & 31) * 4 * 128);   // rows 4 gl .. : tile gl >> 5, row (gl & 31) * 4 in it
     for (int64_t ps = blockIdx.x; ps < passes; ps += gridDim.x, it++) {
       const int s = it % astages;
       mbar_wait_relaxed(&a_empty[s], ((it / astages) & 1) ^ 1);
-      const int64_t row0 = ps * KT_ROWS;
-      unsigned char *stage = smem_raw + (size_t)s * 2 * tile_bytes;
-      for (int rb0 = 0; rb0 < KT_ROWS; rb0 += BATCH * rstep) {
-        const int rb = rb0 + pw * rpp + r_off;
-        float4 v[BATCH];
-#pragma unroll
-        for (int u = 0; u < BATCH; u++) {
-          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (gi[u] >= 0) {
-            const float *src = p.x + gi[u] * (int64_t)d + e;
-            if (vec) {
-              v[u] = ldg_stream4(src);          // read once: keep it out of L1
-            } else {
-              v[u].x = __ldg(src);
-              if (e + 1 < d) v[u].y = __ldg(src + 1);
-              if (e + 2 < d) v[u].z = __ldg(src + 2);
-              if (e + 3 < d) v[u].w = __ldg(src + 3);
-            }
-          }
-        }
-        // the next batch's indices (this pass's, or the first of the next pass) fly under these loads
-        if (rb0 + BATCH * rstep < KT_ROWS) fetch_idx(row0, rb + BATCH * rstep, gi);
-        else if (ps + gridDim.x < passes) fetch_idx((ps + gridDim.x) * KT_ROWS, pw * rpp + r_off, gi);
-#pragma unroll
-        for (int u = 0; u < BATCH; u++) {
-          const int r = rb + u * rstep;
-          if (active && r < KT_ROWS) {
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
-            const int rr = r & (KT_M - 1);
-            unsigned char *dst = stage + (r >> 7) * tile_bytes + kb * KT_KB_BYTES + rr * 128 + ((ch ^ (rr & 7)) << 4) + within;
-            *reinterpret_cast<uint2 *>(dst) = make_uint2(*reinterpret_cast<const unsigned *>(&lo), *reinterpret_cast<const unsigned *>(&hi));
-          }
-        }
-      }
-      fence_proxy_async();
-      mbar_arrive(&a_full[s]);
-    }
+      if (lane == 0) mbar_expect_tx(&a_full[s], 2 * tile_bytes / KT_GATHER_WARPS);   // this warp's share of the two point tiles, every k-block
+      __syncwarp();
+      const uint32_t dst = sA + (uint32_t)s * 2 * tile_bytes + lane_dst;
+      if (on)
+        for (int kb = 0; kb < kblocks; kb++)
+          tma_gather4(dst + kb * KT_KB_BYTES, &tmA, kb * 64, idx[0], idx[1], idx[2], idx[3], &a_full[s]);
+      rows_of(ps + gridDim.x, idx);             // the next pass's row numbers travel while this one is consumed
     }
   } else if (warp == KT_WARP_TMA) {
     // ===================== TMA: centroid tiles (the whole warp walks the loop, one elected lane issues) =====================
@@ -1040,6 +975,13 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   if (encode(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.t_cbf, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return cudaErrorInvalidValue;
+  // the BF16 copy of x, row by row (box = 64 columns x 1 row; tile::gather4 takes four such rows per instruction)
+  CUtensorMap tmA;
+  const cuuint64_t adim[2] = {(cuuint64_t)drow, (cuuint64_t)a.n};
+  const cuuint32_t abox[2] = {64, 1};
+  if (encode(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(a.t_xbf), adim, gstride, abox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return cudaErrorInvalidValue;
   e = cudaMemsetAsync(a.t_work_count, 0, sizeof(unsigned), a.stream);
   if (e != cudaSuccess) return e;
   KtParams p;
@@ -1055,7 +997,7 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t passes = (a.n + KT_ROWS - 1) / KT_ROWS;
-  kern<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmB, p);
+  kern<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmA, tmB, p);
   (*launches)++;
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
 

@@ -112,6 +112,8 @@ struct km_ctx {
   int t_order_age = 0;              // passes since it was built
   float *t_xn = nullptr;            // [n] |x_i|, computed on the first tensor pass after an upload
   bool t_xn_valid = false;
+  void *t_xbf = nullptr;            // [n][64 * kblocks] BF16 copy of x (same lifetime as t_xn)
+  size_t t_xbf_bytes = 0;
   int64_t t_work_n = 0;
   int path_now = 0;                 // KM_PATH_* chosen for the current (points, centroids)
 
@@ -146,6 +148,7 @@ struct KmAssignArgs {
   unsigned *t_hist, *t_work_count, *t_order;
   int *t_work;         // tensor path: worklist of the exact stage
   const float *t_xn;   // tensor path: |x_i| per point
+  const void *t_xbf;   // tensor path: BF16 copy of x, rows padded to 64 * kblocks
   int t_labels_fresh;  // every label is still -1: no point ordering the points by it
   int t_order_reuse;   // keep the index list of an earlier pass (rebuilt every few passes once the run has settled)
   float t_xnmax;       // tensor path: upper bound of |x_i|
@@ -165,6 +168,8 @@ bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_opti
 size_t km_tensor_cbf_bytes(int32_t d, int32_t k);
 size_t km_tensor_h_bytes(int32_t k);
 size_t km_tensor_work_bytes(int64_t n);
+size_t km_tensor_xbf_bytes(int64_t n, int32_t d);
+cudaError_t km_launch_xbf(const float *x, int64_t n, int32_t d, void *xbf, int sm_count, cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           int fine, KmPrune2 *out);
