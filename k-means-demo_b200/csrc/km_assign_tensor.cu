@@ -186,6 +186,12 @@ __device__ __forceinline__ void add2(float &x, float &y, float hx, float hy) {
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
+// The same for a K-major operand WITHOUT swizzle (layout type 0): 8-row x 16-byte core matrices, 8-row groups
+// `sbo` bytes apart, the two 16-byte chunks of a K = 16 step `lbo` bytes apart (canonical layout
+// ((8,m),(T,2)):((1T,SBO),(1,LBO)) of cute's make_umma_desc<Major::K>).
+__device__ __forceinline__ uint64_t umma_desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 at [4,6), a/b format
 // BF16 = 1 at [7,10)/[10,13), both K-major, N>>3 at [17,23), M>>4 at [24,29).
 __device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
@@ -211,7 +217,8 @@ static __host__ __device__ inline size_t kt_smem_bytes(int d) {
 // the BF16 copy of the row, zero beyond d and beyond k.
 __global__ void __launch_bounds__(256) km_tensor_prep_kernel(const float *__restrict__ chi, int k, int d, int kpad,
                                                              float *__restrict__ h, KmState *st,
-                                                             __nv_bfloat16 *__restrict__ cbf, int drow, int fold_col) {
+                                                             __nv_bfloat16 *__restrict__ cbf, int drow, int fold_col,
+                                                             __nv_bfloat16 *__restrict__ hfold) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= kpad) return;
   float s = 0.f;
@@ -235,6 +242,16 @@ __global__ void __launch_bounds__(256) km_tensor_prep_kernel(const float *__rest
       cbf[(int64_t)warp * drow + fold_col] = b0;
       cbf[(int64_t)warp * drow + fold_col + 1] = b1;
       cbf[(int64_t)warp * drow + fold_col + 2] = b2;
+    }
+    if (hfold) {           // foldx: the same three pieces as a 16-byte row of their own (the extra K-step's centroid operand)
+      const float hf = warp < k ? hv : -3.0e38f;
+      const __nv_bfloat16 b0 = __float2bfloat16_rn(hf);
+      const float r1 = warp < k ? hf - __bfloat162float(b0) : 0.f;
+      const __nv_bfloat16 b1 = __float2bfloat16_rn(r1);
+      const __nv_bfloat16 b2 = __float2bfloat16_rn(r1 - __bfloat162float(b1));
+      const __nv_bfloat16 z = __float2bfloat16_rn(0.f);
+      __nv_bfloat16 *o = hfold + (int64_t)warp * 8;
+      o[0] = b0; o[1] = b1; o[2] = b2; o[3] = z; o[4] = z; o[5] = z; o[6] = z; o[7] = z;
     }
   }
 }
@@ -403,6 +420,7 @@ struct KtParams {
   const float *xn;         // [n] |x_i| (binary32, km_row_norm_kernel)
   const float *h;          // [kpad] -|chi_j|^2 / 2, -inf beyond k
   int h_in_smem;           // the launcher found room for a shared-memory copy of h
+  int foldx;               // h rides in one extra K-step whose operands are small no-swizzle tiles (rows without spare columns)
   const KmState *st;       // st->cnmax2 = max_j |chi_j|^2
   float xnmax;             // upper bound of |x_i| over the job
   int *work;               // worklist entries, KT_WORK_INTS ints each
@@ -463,10 +481,12 @@ __device__ __noinline__ int kt_collect(int2 *lst, int row, int cnt, float thr, f
 // HSMEM: h has a copy in shared memory, read with ld.shared (its own queue — a generic or global load of h
 // would wait in line behind the producers' stream of point loads)
 template <bool HSMEM, bool FOLD>
-__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const KtParams p) {
+__global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                                         const __grid_constant__ CUtensorMap tmH, const KtParams p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const int d = p.d, kblocks = kt_kblocks(d), bstages = kt_bstages(d);
-  const int nks = ((d + 15) >> 4) + (FOLD ? 1 : 0);             // K = 16 MMA steps over the (zero-padded) dimension [+ the h columns]
+  const bool foldx = FOLD && p.foldx != 0;
+  const int nks = ((d + 15) >> 4) + ((FOLD && !foldx) ? 1 : 0);  // K = 16 MMA steps over the (zero-padded) dimension [+ the h columns]
   const uint32_t tile_bytes = (uint32_t)kblocks * KT_KB_BYTES;   // one 128-row operand tile
   const int astages = kt_astages(d);
   const uint32_t sA = smem_u32(smem_raw);                        // [astages][2 tiles]
@@ -482,6 +502,16 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
   if (HSMEM && !FOLD)
     for (int j = threadIdx.x; j < kpad_h; j += KT_THREADS) hs[j] = p.h[j];
   const uint32_t hs_addr = smem_u32(hs);
+  // foldx: the extra K-step's operands, no swizzle, rows 16 bytes apart.  Chunk 0 of the point side is the same for
+  // every point ({1, 1, 1, 0...}: it multiplies the three BF16 pieces of h), chunk 0 of the centroid side arrives by
+  // TMA with each centroid tile, chunk 1 of both is one block of zeros.
+  const uint32_t sAf = hs_addr, sBf = sAf + 2048, sZ = sBf + 2048 * (uint32_t)bstages;
+  if (foldx) {
+    for (int r = threadIdx.x; r < KT_M; r += KT_THREADS) {
+      reinterpret_cast<uint4 *>(hs)[r] = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
+      reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(hs) + 2048 * (1 + bstages))[r] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // (the point tiles arrive whole by TMA from the BF16 copy of x: zero padding and — FOLD — the 1.0 columns are part of its rows)
@@ -569,9 +599,10 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
         if (tt >= ntiles) tt -= ntiles;
         mbar_wait_relaxed(&b_empty[sb], ((g / bstages) & 1) ^ 1);
         if (elect_one_sync()) {
-          mbar_expect_tx(&b_full[sb], tile_bytes);
+          mbar_expect_tx(&b_full[sb], tile_bytes + (foldx ? 2048u : 0u));
           for (int kbi = 0; kbi < kblocks; kbi++)
             tma_load_2d(sB + sb * tile_bytes + kbi * KT_KB_BYTES, &tmB, kbi * 64, tt * KT_N, &b_full[sb]);
+          if (foldx) tma_load_2d(sBf + sb * 2048, &tmH, 0, tt * KT_N, &b_full[sb]);   // the tile's 128 x {h_hi, h_mid, h_lo, 0 x 5}
         }
         __syncwarp();
       }
@@ -603,6 +634,9 @@ __global__ void __launch_bounds__(KT_THREADS, 1) km_tensor_coarse_kernel(const _
                 umma_bf16(tacc, adesc + koff, bdesc + koff, idesc, ks != 0);
               }
             }
+            // + h: one more K = 16 step, {1, 1, 1, 0...} against the tile's {h_hi, h_mid, h_lo, 0...}
+            if (foldx)
+              umma_bf16(tacc, umma_desc_nosw(sAf, sZ - sAf, 128), umma_desc_nosw(sBf + sb * 2048, sZ - (sBf + sb * 2048), 128), idesc, 1);
           }
           umma_commit(&b_empty[sb]);          // the centroid tile may be overwritten once these MMAs are done
           umma_commit(&acc_full[b]);          // ... and the epilogue may read the accumulators
@@ -913,7 +947,8 @@ bool km_tensor_path_supported(int32_t d, int32_t k, int dtype, int max_smem_opti
 }
 
 static int kt_kpad(int32_t k) { return ((k + KT_N - 1) / KT_N) * KT_N; }
-size_t km_tensor_cbf_bytes(int32_t d, int32_t k) { return (size_t)kt_kpad(k) * kt_kblocks(d) * 64 * sizeof(__nv_bfloat16); }
+// the BF16 centroid rows, then one 16-byte row per centroid with the three BF16 pieces of h (foldx)
+size_t km_tensor_cbf_bytes(int32_t d, int32_t k) { return (size_t)kt_kpad(k) * (kt_kblocks(d) * 64 + 8) * sizeof(__nv_bfloat16); }
 size_t km_tensor_h_bytes(int32_t k) { return (size_t)kt_kpad(k) * sizeof(float); }
 size_t km_tensor_work_bytes(int64_t n) { return (size_t)(n > 0 ? n : 1) * KT_WORK_INTS * sizeof(int); }
 
@@ -941,8 +976,11 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   cudaError_t e = cudaMemsetAsync(&a.state->cnmax2, 0, sizeof(float), a.stream);
   if (e != cudaSuccess) return e;
   const bool fold = kt_fold(a.d);
+  __nv_bfloat16 *hfold = (__nv_bfloat16 *)a.t_cbf + (size_t)kpad * drow;
+  const bool foldx = !fold && kt_smem_bytes(a.d) + 2048 * (2 + kt_bstages(a.d)) + 1024 <= (size_t)a.max_smem_optin;
   km_tensor_prep_kernel<<<(kpad * 32 + 255) / 256, 256, 0, a.stream>>>(a.chi, a.k, a.d, kpad, a.t_cn, a.state,
-                                                                       (__nv_bfloat16 *)a.t_cbf, drow, fold ? ((a.d + 15) & ~15) : -1);
+                                                                       (__nv_bfloat16 *)a.t_cbf, drow, fold ? ((a.d + 15) & ~15) : -1,
+                                                                       foldx ? hfold : nullptr);
   (*launches)++;
   if (a.n == 0) return cudaGetLastError();
   if (a.n >= ((int64_t)1 << 31)) return cudaErrorInvalidValue;   // worklist rows are 32-bit
@@ -982,6 +1020,14 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   if (encode(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(a.t_xbf), adim, gstride, abox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return cudaErrorInvalidValue;
+  // the three BF16 pieces of h, a 16-byte row per centroid, no swizzle (foldx)
+  CUtensorMap tmH;
+  const cuuint64_t hdim[2] = {8, (cuuint64_t)kpad};
+  const cuuint64_t hstride[1] = {16};
+  const cuuint32_t hbox[2] = {8, KT_N};
+  if (encode(&tmH, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, hfold, hdim, hstride, hbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return cudaErrorInvalidValue;
   e = cudaMemsetAsync(a.t_work_count, 0, sizeof(unsigned), a.stream);
   if (e != cudaSuccess) return e;
   KtParams p;
@@ -990,14 +1036,16 @@ cudaError_t km_launch_assign_tensor(const KmAssignArgs &a, int64_t *launches) {
   p.st = a.state; p.xnmax = a.t_xnmax; p.work = a.t_work; p.work_count = a.t_work_count;
   p.all_to_work = a.incremental ? 0 : 1;
   size_t smem = kt_smem_bytes(a.d);
-  p.h_in_smem = !fold && smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
+  p.foldx = foldx ? 1 : 0;
+  if (foldx) smem += 2048 * (2 + kt_bstages(a.d));
+  p.h_in_smem = !fold && !foldx && smem + (size_t)kpad * sizeof(float) + 1024 <= (size_t)a.max_smem_optin;
   if (p.h_in_smem) smem += (size_t)kpad * sizeof(float);
-  auto kern = fold ? km_tensor_coarse_kernel<false, true>
+  auto kern = (fold || foldx) ? km_tensor_coarse_kernel<false, true>
                    : (p.h_in_smem ? km_tensor_coarse_kernel<true, false> : km_tensor_coarse_kernel<false, false>);
   e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t passes = (a.n + KT_ROWS - 1) / KT_ROWS;
-  kern<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmA, tmB, p);
+  kern<<<(int)(passes < a.sm_count ? passes : a.sm_count), KT_THREADS, smem, a.stream>>>(tmA, tmB, tmH, p);
   (*launches)++;
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
 
