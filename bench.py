@@ -489,23 +489,34 @@ def run_ours(args, wl):
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     c_host = np.empty((k, d), dtype=np.float64)
 
-    def e2e_step():
+    byte_labels = k <= 255                     # km_get_labels_u8: a quarter of the label bytes
+    l8buf, _ = km.host_alloc(max(16, n))
+    labels8_host = l8buf[:n].view(np.uint8)
+
+    def e2e_step(narrow):
         st.upload_points_raw(xaddr, n, d)      # H2D: the step's points, from pinned memory
         st.set_centroids(c0)                   # H2D: the step's centroids
         s = st.step()                          # one Lloyd iteration
-        st.labels(out=labels_host)             # D2H: labels
+        if narrow:
+            st.labels(out=labels8_host)        # D2H: labels as bytes
+        else:
+            st.labels(out=labels_host)         # D2H: labels as int32
         st.centroids(out=c_host)               # D2H: updated centroids
         return s
 
-    for _ in range(2):
-        e2e_step()
-    job.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    job.barrier()
-    e2e_s = job.max_over_ranks(time.perf_counter() - t0)
-    e2e_value = n_total * e2e_steps / e2e_s
+    def e2e_time(narrow):
+        for _ in range(2):
+            e2e_step(narrow)
+        job.barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step(narrow)
+        job.barrier()
+        return n_total * e2e_steps / job.max_over_ranks(time.perf_counter() - t0)
+
+    e2e_i32 = e2e_time(False)
+    e2e_value = e2e_time(True) if byte_labels else e2e_i32
+    u8_ok = bool(np.array_equal(labels8_host, labels_host.astype(np.uint8))) if byte_labels else None
     # the whole-job call a user makes (upload once, iterate, download once) — and the parity record:
     # labels / centroids / iteration count of this run must be the same bits at every GPU count
     job.barrier()
@@ -518,8 +529,10 @@ def run_ours(args, wl):
     job.barrier()
     run_s = job.max_over_ranks(time.perf_counter() - t0)
     e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": (n * d * 4 + k * d * 8) * world,
-           "d2h_bytes_per_step": (n * 4 + k * d * 8 + 64) * world, "steps": e2e_steps,
-           "call": "km_upload_points(pinned)+km_set_centroids+km_step+km_get_labels+km_get_centroids per step",
+           "d2h_bytes_per_step": (n * (1 if byte_labels else 4) + k * d * 8 + 64) * world, "steps": e2e_steps,
+           "call": "km_upload_points(pinned)+km_set_centroids+km_step+" + ("km_get_labels_u8" if byte_labels else "km_get_labels") +
+                   "+km_get_centroids per step",
+           "value_with_int32_labels": e2e_i32, "byte_labels_equal_int32_labels": u8_ok,
            "run_value": n_total * rs["iterations"] / run_s, "run_iterations": rs["iterations"], "run_seconds": run_s,
            "run_call": "km_upload_points+km_set_centroids+km_run(max_iter)+km_get_labels+km_get_centroids, once"}
     parity = None

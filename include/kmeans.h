@@ -171,7 +171,11 @@ KM_API km_status km_step_async(km_ctx *ctx);
 KM_API km_status km_stats_fetch(km_ctx *ctx, km_stats *stats);
 
 /* ---- a5: run to convergence (analog: #iter -> yMeta.iteration app.mjs:286-288,498-508) */
-/* labels reset to -1; repeat { assign; it++; if (changed==0 || it==max_iter) break; update } */
+/* labels reset to -1; repeat { assign; it++; if (changed==0 || it==max_iter) break; update }.
+ * A single-rank job on the small-d path whose points fit in shared memory (n * (4d + 4) bytes over the
+ * SMs, k * d <= 32, KM_UPDATE_INCREMENTAL, profile_kernels off) runs the whole loop in ONE cooperative
+ * launch with the points resident on the chip; every other job is issued iteration by iteration.  Same
+ * results either way. */
 KM_API km_status km_run(km_ctx *ctx, int32_t max_iter, km_stats *stats);
 /* forget labels and sums (the next assign sees every label as changed) */
 KM_API km_status km_reset_labels(km_ctx *ctx);
@@ -187,6 +191,10 @@ KM_API km_status km_set_update_mode(km_ctx *ctx, int32_t update_mode);
  * pointer may be NULL).  No counterpart in the reference. */
 KM_API km_status km_get_shape(const km_ctx *ctx, int64_t *n_local, int64_t *n_total, int32_t *d, int32_t *k);
 KM_API km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n);   /* this rank's shard */
+/* the same labels as bytes, for k <= 255 (255 = never assigned): a quarter of the device-to-host
+ * traffic of km_get_labels.  The first call per shard size allocates an n-byte device buffer.
+ * No counterpart in the reference (card.cluster is a JS number, app.mjs:143-156). */
+KM_API km_status km_get_labels_u8(km_ctx *ctx, uint8_t *out, int64_t n);
 KM_API km_status km_get_centroids(km_ctx *ctx, double *out);            /* k*d, row-major */
 /* a6: per-cluster member counts of the whole job (analog: snapshotMetrics counts
  * app.mjs:481-496) */

@@ -63,6 +63,7 @@ PROTOTYPES = {
     "km_run": (_i32, [_vp, _i32, C.POINTER(Stats)]),
     "km_reset_labels": (_i32, [_vp]),
     "km_set_update_mode": (_i32, [_vp, _i32]),
+    "km_get_labels_u8": (_i32, [_vp, _vp, _i64]),
     "km_comm_info": (_i32, [_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32)]),
     "km_get_shape": (_i32, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i32), C.POINTER(_i32)]),
     "km_get_labels": (_i32, [_vp, _vp, _i64]),

@@ -188,12 +188,20 @@ class KMeansState:
         self._check(self._lib.km_set_update_mode(self._h, mode))
 
     # -- results
-    def labels(self, out=None):
+    def labels(self, out=None, dtype=np.int32):
+        """This rank's labels in the caller's row order; dtype=np.uint8 (k <= 255, 255 = never assigned)
+        brings them home as bytes."""
+        dtype = np.dtype(dtype) if out is None else out.dtype
+        if dtype not in (np.dtype(np.int32), np.dtype(np.uint8)):
+            raise TypeError("labels are int32 or uint8")
         if out is None:
-            out = np.empty(self.n, dtype=np.int32)
+            out = np.empty(self.n, dtype=dtype)
         else:
-            self._check_out(out, self.n, np.int32, "labels")
-        self._check(self._lib.km_get_labels(self._h, _ptr(out), self.n))
+            self._check_out(out, self.n, dtype, "labels")
+        if dtype == np.dtype(np.uint8):
+            self._check(self._lib.km_get_labels_u8(self._h, _ptr(out), self.n))
+        else:
+            self._check(self._lib.km_get_labels(self._h, _ptr(out), self.n))
         return out
 
     def centroids(self, out=None):

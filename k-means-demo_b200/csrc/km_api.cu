@@ -1420,6 +1420,22 @@ extern "C" km_status km_get_labels(km_ctx *ctx, int32_t *out, int64_t n) {
   return copy_d2h(ctx, out, ctx->labels, (size_t)n * sizeof(int32_t));
 }
 
+extern "C" km_status km_get_labels_u8(km_ctx *ctx, uint8_t *out, int64_t n) {
+  KM_BIND(ctx);
+  if (!ctx->have_points) return fail(ctx, KM_ERR_STATE, "no points");
+  if (n != ctx->n || (n > 0 && !out)) return fail(ctx, KM_ERR_INVALID_ARG, "km_get_labels_u8: n must equal the shard size");
+  if (ctx->have_centroids && ctx->k > 255) return fail(ctx, KM_ERR_UNSUPPORTED, "km_get_labels_u8: k must be <= 255");
+  if (n == 0) return KM_OK;
+  if (ctx->narrow_n < n) {
+    if (ctx->narrow_buf) cudaFree(ctx->narrow_buf);
+    ctx->narrow_buf = nullptr; ctx->narrow_n = 0;
+    KM_CUDA(ctx, cudaMalloc(&ctx->narrow_buf, (size_t)n));
+    ctx->narrow_n = n;
+  }
+  KM_CUDA(ctx, km_narrow_labels(ctx->labels, ctx->perm, n, ctx->narrow_buf, ctx->sm_count, ctx->stream, &ctx->launches));
+  return copy_d2h(ctx, out, ctx->narrow_buf, (size_t)n);
+}
+
 extern "C" km_status km_get_centroids(km_ctx *ctx, double *out) {
   KM_BIND(ctx);
   if (!ctx->have_centroids || !out) return fail(ctx, KM_ERR_STATE, "no centroids");

@@ -64,6 +64,8 @@ struct km_ctx {
   cudaEvent_t ring_ev[KM_RING];
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int64_t launches = 0;
+  unsigned char *narrow_buf = nullptr;   // [n] labels as bytes (km_get_labels_u8), allocated by its first call per upload shape
+  int64_t narrow_n = 0;
   int coop_ok = 0;                  // device supports cooperative launches (km_resident.cu)
   int32_t host_it = 0;              // assign steps issued since the last label reset
   int32_t last_path = 0;
@@ -173,6 +175,8 @@ cudaError_t km_launch_xbf(const float *x, int64_t n, int32_t d, void *xbf, int s
 cudaError_t km_launch_row_norms(const float *x, int64_t n, int32_t d, float *xn, int sm_count, cudaStream_t s, int64_t *launches);
 bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_points, int sm_count, const double bbox[4],
                           int fine, KmPrune2 *out);
+cudaError_t km_narrow_labels(const int32_t *labels, const unsigned *perm, int64_t n, unsigned char *out_dev, int sm_count,
+                             cudaStream_t s, int64_t *launches);
 cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, int64_t len,
                                      unsigned long long epoch, long long *out, int *err, cudaStream_t s, int64_t *launches);
 // km_resident.cu: the whole km_run loop in one cooperative launch for jobs that fit in shared memory

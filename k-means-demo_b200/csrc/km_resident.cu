@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
   for (int e = threadIdx.x; e < k * D; e += KR_THREADS) cd[e] = p.C_in[e];
   for (int e = threadIdx.x; e < (int)L.scal; e += KR_THREADS) Sloc[e] = 0;
   KR_STAMP();   // (after the loads are issued; they complete at the first barrier)
-  long long changed = 0;
+  long long changed = 0, rescored = 0;
   long long *wtab = tab + (size_t)(threadIdx.x >> 5) * L.len;      // this warp's own delta table: no atomics between warps
   KmBlockTab T;
   T.L = L;
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
     // ---- a3: assignment of this block's points.  Binary32 differences first; the oracle's binary64
     // arithmetic only where the two best are closer than the filter's error bound.
     KR_STAMP();   // loop top synced
-    long long mine = 0;
+    long long mine = 0, resc = 0;
     int q_count = 0;                                 // warp-uniform: moves waiting in this warp's queue
     auto drain = [&](int base, int m) {              // lane l carries out queued move base + l
       __syncwarp();
@@ -160,6 +160,7 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
         if (!((b2[q] - b1[q]) > fmaf(p.rho2, b2[q], p.tau2))) {      // too close to call in binary32 (or not finite)
           double best = __longlong_as_double(0x7FF0000000000000LL);
           nw = 0;
+          if (in) resc++;
           for (int j = 0; j < k; j++) {
             const double dj = km_dist2_f64(xv[q], cd + j * D, D);
             if (dj < best) { best = dj; nw = j; }
@@ -217,6 +218,8 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
     KR_STAMP();   // assign done (thread 0)
     mine = km_warp_sum_ll(mine);
     if (lane == 0 && mine != 0) wtab[L.scal + KM_ACC_CHANGED] += mine;
+    resc = km_warp_sum_ll(resc);
+    if (lane == 0 && resc != 0) wtab[L.scal + KM_ACC_RESCORED] += resc;
     __syncthreads();
     long long *Dw = p.Dt[it % 3];
     // the warps' tables -> one RED per non-zero entry; 8 lanes share an entry (two tables each)
@@ -235,6 +238,7 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
     it++;
     for (int e = threadIdx.x; e < (int)L.scal; e += KR_THREADS) Sloc[e] += __ldcg(Dw + e);
     changed = __ldcg(Dw + L.scal + KM_ACC_CHANGED);
+    rescored = __ldcg(Dw + L.scal + KM_ACC_RESCORED);
     if (blockIdx.x == 0) {                         // the table of the iteration after the next one
       long long *Dz = p.Dt[(it + 1) % 3];
       for (int e = threadIdx.x; e < (int)L.len; e += KR_THREADS) Dz[e] = 0;
@@ -284,7 +288,7 @@ __global__ void __launch_bounds__(KR_THREADS, 1) km_resident_kernel(const KmResi
       sl.it = it;
       sl.changed = changed;
       sl.inertia = km_inertia_from_limbs(p.Ta, p.Tb, p.QBt, p.qt, ga, gb, p.QBg, p.qg);
-      sl.rescored = 0;
+      sl.rescored = rescored;
       sl.updated = 0;
       sl.pad = 0;
       p.ring[0] = sl;

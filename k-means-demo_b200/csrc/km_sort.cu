@@ -108,6 +108,38 @@ cudaError_t km_unpermute_labels(const int32_t *labels_sorted, const unsigned *pe
   return cudaGetLastError();
 }
 
+// labels as bytes (k <= 255; 255 = never assigned), in the caller's row order: a quarter of the bytes to bring home
+__global__ void __launch_bounds__(256) km_narrow_labels_kernel(const int32_t *__restrict__ labels, const unsigned *__restrict__ perm,
+                                                               int64_t n, unsigned char *__restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (perm) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+      const int l = labels[i];
+      out[perm[i]] = (unsigned char)(l < 0 ? 255 : l);
+    }
+  } else {
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q * 4 < n; q += stride) {
+      unsigned w = 0;
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const int64_t i = q * 4 + t;
+        const int l = i < n ? labels[i] : 0;
+        w |= (unsigned)(l < 0 ? 255 : (l & 255)) << (8 * t);
+      }
+      if (q * 4 + 4 <= n) reinterpret_cast<unsigned *>(out)[q] = w;
+      else for (int t = 0; q * 4 + t < n; t++) out[q * 4 + t] = (unsigned char)(w >> (8 * t));
+    }
+  }
+}
+
+cudaError_t km_narrow_labels(const int32_t *labels, const unsigned *perm, int64_t n, unsigned char *out_dev, int sm_count,
+                             cudaStream_t s, int64_t *launches) {
+  if (n == 0) return cudaSuccess;
+  km_narrow_labels_kernel<<<grid_for(perm ? n : (n + 3) / 4, sm_count), 256, 0, s>>>(labels, perm, n, out_dev);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
 cudaError_t km_unpermute_rows2(const float *x_sorted, const unsigned *perm, int64_t n, int64_t i0, int64_t cnt,
                                float *out_dev, int sm_count, cudaStream_t s, int64_t *launches) {
   if (n == 0 || cnt == 0) return cudaSuccess;

@@ -396,6 +396,28 @@ def test_board_export_import_round_trip(km):
     st2.close()
 
 
+def test_labels_as_bytes(km):
+    # km_get_labels_u8: the same labels, a byte each — plain store, cell-sorted store, ragged n, fresh labels, k > 255
+    for n, d, k, kw in [(10_003, 3, 7, {}), (40_001, 2, 64, {"prune_min_points": 1}), (5, 2, 2, {})]:
+        x = oracle.gen_blobs(21, n, d, k)
+        c0 = oracle.forgy_init(x, k, 3)
+        with km.KMeansState(**kw) as st:
+            st.upload_points(x)
+            st.set_centroids(c0)
+            assert np.all(st.labels(dtype=np.uint8) == 255)          # never assigned
+            st.run(12)
+            a, b = st.labels(), st.labels(dtype=np.uint8)
+            assert b.dtype == np.uint8 and np.array_equal(a, b.astype(np.int32))
+            out = np.empty(n, dtype=np.uint8)
+            assert st.labels(out=out) is out and np.array_equal(out, b)
+    x = oracle.gen_blobs(22, 2000, 2, 300)
+    with km.KMeansState() as st:
+        st.upload_points(x)
+        st.set_centroids(oracle.forgy_init(x, 300, 3))
+        with pytest.raises(km.KMeansError):
+            st.labels(dtype=np.uint8)
+
+
 def test_errors(km):
     L = km._lib
     with km.KMeansState() as st:
