@@ -994,6 +994,7 @@ static void fill_assign_args(km_ctx *ctx, KmAssignArgs &a) {
   a.labels = ctx->labels; a.c64 = ctx->c64; a.chi = ctx->chi; a.clo = ctx->clo;
   a.acc = ctx->acc; a.state = ctx->state;
   a.incremental = ctx->cfg.update_mode == KM_UPDATE_INCREMENTAL;
+  a.all_push = (!a.incremental || ctx->labels_fresh) ? 1 : 0;
   a.exact_inertia = ctx->cfg.exact_inertia;
   a.sm_count = ctx->sm_count; a.max_smem_optin = ctx->max_smem_optin; a.stream = ctx->stream;
   a.hilo = ctx->use_hilo ? 1 : 0;

@@ -320,6 +320,93 @@ __device__ __noinline__ void km_small_drain(long long *tab, int k, const unsigne
   km_move_point(T, xm, D, (int)e[D + 1], (int)e[D], scale_a, scale_b);
 }
 
+// The same for a full batch of 32 queued moves, called by the whole warp.  On the cell-sorted store (and on
+// any first or full-update pass over spatially coherent points) most of a batch shares one (from, to) pair:
+// those lanes add their limbs up among themselves — each 64-bit limb as three 21/21/22-bit pieces through the
+// 32-bit warp reduction, sums modulo 2^64 being exact whatever the split — and lane 0 alone touches the table.
+// Thirty-two lanes hammering one table entry with 64-bit shared-memory atomics (compare-and-swap loops) is
+// the slowest thing this kernel can do; this is what made a pass that accumulates every point 10x a
+// steady-state one.  Lanes with another pair move their point by themselves as before.
+template <int D>
+__device__ __noinline__ void km_small_drain_warp(long long *tab, int k, const unsigned *e, double scale_a, double scale_b) {
+  KmBlockTab T;
+  T.L = km_acc_layout(k, D);
+  T.tab = tab;
+  float xm[D];
+#pragma unroll
+  for (int t = 0; t < D; t++) xm[t] = __uint_as_float(e[t]);
+  const int from = (int)e[D], to = (int)e[D + 1];
+  const int from0 = __shfl_sync(0xffffffffu, from, 0), to0 = __shfl_sync(0xffffffffu, to, 0);
+  const bool same = from == from0 && to == to0;
+  const unsigned grp = __ballot_sync(0xffffffffu, same);
+  if (__popc(grp) < 8) {                       // warp-uniform: not worth the reductions
+    km_move_point(T, xm, D, to, from, scale_a, scale_b);
+    return;
+  }
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int t = 0; t < D; t++) {
+    long long a = 0, b = 0;
+    if (same) km_fixed_split((double)xm[t], scale_a, scale_b, a, b);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const unsigned long long v = (unsigned long long)(h == 0 ? a : b);
+      const unsigned r0 = __reduce_add_sync(0xffffffffu, (unsigned)(v & 0x1FFFFFu));
+      const unsigned r1 = __reduce_add_sync(0xffffffffu, (unsigned)((v >> 21) & 0x1FFFFFu));
+      const unsigned r2 = __reduce_add_sync(0xffffffffu, (unsigned)(v >> 42));
+      if (lane == 0) {
+        const long long tot = (long long)((unsigned long long)r0 + ((unsigned long long)r1 << 21) + ((unsigned long long)r2 << 42));
+        const int64_t off = (h == 0 ? T.L.sa : T.L.sb) + t;
+        km_atomic_add_ll(tab + off + (int64_t)to0 * D, tot);
+        if (from0 >= 0) km_atomic_add_ll(tab + off + (int64_t)from0 * D, -tot);
+      }
+    }
+  }
+  if (lane == 0) {
+    km_atomic_add_ll(tab + T.L.cnt + to0, (long long)__popc(grp));
+    if (from0 >= 0) km_atomic_add_ll(tab + T.L.cnt + from0, -(long long)__popc(grp));
+  }
+  if (!same) km_move_point(T, xm, D, to, from, scale_a, scale_b);
+}
+
+// one move from registers (the odd point of a round whose points otherwise share one target)
+template <int D>
+__device__ __noinline__ void km_small_move_one(long long *tab, int k, KmRow<D> x, int from, int to, double scale_a, double scale_b) {
+  KmBlockTab T;
+  T.L = km_acc_layout(k, D);
+  T.tab = tab;
+  km_move_point(T, x.v, D, to, from, scale_a, scale_b);
+}
+// per-lane partial sums of points that all go from `from0` to `to0` -> the warp's total -> lane 0 adds it to the table
+template <int D>
+struct KmLimbs { long long a[D], b[D]; };
+template <int D>
+__device__ __noinline__ void km_small_warp_add(long long *tab, int k, KmLimbs<D> s, int c, int from0, int to0) {
+  const KmAccLayout L = km_acc_layout(k, D);
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int t = 0; t < D; t++) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const unsigned long long v = (unsigned long long)(h == 0 ? s.a[t] : s.b[t]);
+      const unsigned r0 = __reduce_add_sync(0xffffffffu, (unsigned)(v & 0x1FFFFFu));
+      const unsigned r1 = __reduce_add_sync(0xffffffffu, (unsigned)((v >> 21) & 0x1FFFFFu));
+      const unsigned r2 = __reduce_add_sync(0xffffffffu, (unsigned)(v >> 42));
+      if (lane == 0) {
+        const long long tot = (long long)((unsigned long long)r0 + ((unsigned long long)r1 << 21) + ((unsigned long long)r2 << 42));
+        const int64_t off = (h == 0 ? L.sa : L.sb) + t;
+        km_atomic_add_ll(tab + off + (int64_t)to0 * D, tot);
+        if (from0 >= 0) km_atomic_add_ll(tab + off + (int64_t)from0 * D, -tot);
+      }
+    }
+  }
+  const int ctot = __reduce_add_sync(0xffffffffu, c);
+  if (lane == 0 && ctot != 0) {
+    km_atomic_add_ll(tab + L.cnt + to0, (long long)ctot);
+    if (from0 >= 0) km_atomic_add_ll(tab + L.cnt + from0, -(long long)ctot);
+  }
+}
+
 // Block 0, prologue: the inertia of the pending pass from the sums (km_common.cuh):
 // this warp's share of the terms c (2S - n c) over the merged sums and the centroids that pass
 // used (C_in), left in sg[warp][0..1].  Kept out of line so its double-double arithmetic costs
@@ -344,7 +431,7 @@ __device__ __noinline__ void km_small_inertia_terms(const long long *S_in, const
   if ((threadIdx.x & 31) == 0) { sg[threadIdx.x >> 5][0] = ga; sg[threadIdx.x >> 5][1] = gb; }
 }
 
-template <int D, bool HILO, bool PRUNE, bool SORTED>
+template <int D, bool HILO, bool PRUNE, bool SORTED, bool ALLPUSH>
 __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(const KmSmallParams p) {
   static_assert(!SORTED || PRUNE, "the cell-sorted store belongs to the pruned path");
   static_assert(!PRUNE || D == 2, "candidate pruning is built for d == 2");
@@ -679,7 +766,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     auto tail = [&](auto full_tag) {
       constexpr bool FULL = decltype(full_tag)::value;
       int newlab[PPT];
-      bool anypush = false;
+      bool anypush = false, allpush = true;
       if (PRUNE && FULL && one_candidate) {
         // whole warp, one candidate: nothing to compare, nothing to measure (the inertia comes
         // from the sums) — only a look at the old labels
@@ -690,6 +777,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           const bool moved = lab != cur.old[q];
           changed += moved ? 1 : 0;
           anypush |= p.incremental ? moved : true;
+          allpush &= p.incremental ? moved : true;
         }
       } else {
 #pragma unroll
@@ -718,10 +806,44 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           const bool moved = lab != cur.old[q];
           changed += moved ? 1 : 0;
           anypush |= live && (p.incremental ? moved : true);
+          allpush &= live && (p.incremental ? moved : true);
         }
       }
       // ---- commit.  Most rounds of a converging run re-label nobody: one vote settles that.
       if (!__any_sync(0xffffffffu, anypush)) return;
+      if (ALLPUSH && __all_sync(0xffffffffu, allpush)) {
+        // Every point of the round moves (a first pass, the full-update mode; this branch exists only in the
+        // instantiation the host picks for such passes, so the steady-state kernel pays no registers for it).
+        // Nearly all of them go the same way as lane 0's first point (the store is cell-sorted; a first pass is
+        // spatially coherent anyhow): each lane adds those up in registers, the warp adds the lanes up with
+        // reductions, lane 0 touches the table; the odd ones out move by themselves.
+        const int to0 = __shfl_sync(0xffffffffu, newlab[0], 0);
+        const int from0 = p.incremental ? __shfl_sync(0xffffffffu, cur.old[0], 0) : -1;
+        KmLimbs<D> acc;
+#pragma unroll
+        for (int t = 0; t < D; t++) { acc.a[t] = 0; acc.b[t] = 0; }
+        int c = 0;
+#pragma unroll
+        for (int q = 0; q < PPT; q++) {
+          KmRow<D> row;
+#pragma unroll
+          for (int m = 0; m < NP; m++) unpk2(cur.xq[q][m], row.v[2 * m], row.v[2 * m + 1]);
+          if (D == 1 || TAIL) row.v[D - 1] = cur.xs[q];
+          const int fr = p.incremental ? cur.old[q] : -1;
+          if (newlab[q] == to0 && fr == from0) {
+#pragma unroll
+            for (int t = 0; t < D; t++) {
+              long long a, b;
+              km_fixed_split((double)row.v[t], scale_a, scale_b, a, b);
+              acc.a[t] += a; acc.b[t] += b;
+            }
+            c++;
+          } else {
+            km_small_move_one<D>(T.tab, k, row, fr, newlab[q], scale_a, scale_b);
+          }
+        }
+        km_small_warp_add<D>(T.tab, k, acc, c, from0, to0);
+      } else
 #pragma unroll
       for (int q = 0; q < PPT; q++) {
         bool live = true;
@@ -745,7 +867,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
           q_count += __popc(bal);
           __syncwarp();
           if (q_count >= 32) {
-            km_small_drain<D>(T.tab, k, qbuf + ((q_head + lane) & (QCAP - 1)) * QW, scale_a, scale_b);
+            km_small_drain_warp<D>(T.tab, k, qbuf + ((q_head + lane) & (QCAP - 1)) * QW, scale_a, scale_b);
             q_head = (q_head + 32) & (QCAP - 1);
             q_count -= 32;
             __syncwarp();
@@ -810,8 +932,8 @@ bool km_small_path_supported(int32_t d, int32_t k, int dtype, int max_smem_optin
   return small_centroid_smem(d, k, true) + 4096 <= (size_t)max_smem_optin / 2;
 }
 
-template <int D, bool HILO, bool PRUNE, bool SORTED>
-static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
+template <int D, bool HILO, bool PRUNE, bool SORTED, bool ALLPUSH>
+static cudaError_t launch_small_ap(const KmAssignArgs &a, int64_t *launches) {
   const KmAccLayout L = km_acc_layout(a.k, D);
   size_t smem = small_centroid_smem(D, a.k, HILO);
   KmSmallParams p;
@@ -838,7 +960,7 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
     if (!p.sorted) smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);   // the block builds its own copy
   }
   smem += (size_t)(KM_SMALL_THREADS / 32) * 64 * (D + 2) * sizeof(unsigned);   // per-warp move queues
-  auto kern = km_assign_small_kernel<D, HILO, PRUNE, SORTED>;
+  auto kern = km_assign_small_kernel<D, HILO, PRUNE, SORTED, ALLPUSH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -885,6 +1007,13 @@ static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
   kern<<<grid, KM_SMALL_THREADS, smem, a.stream>>>(p);
   (*launches)++;
   return cudaGetLastError();
+}
+
+// a pass in which every point is accumulated (labels all -1, or the full-update mode) runs the instantiation with
+// the warp-aggregated commit; the steady-state instantiation does not carry that code
+template <int D, bool HILO, bool PRUNE, bool SORTED>
+static cudaError_t launch_small(const KmAssignArgs &a, int64_t *launches) {
+  return a.all_push ? launch_small_ap<D, HILO, PRUNE, SORTED, true>(a, launches) : launch_small_ap<D, HILO, PRUNE, SORTED, false>(a, launches);
 }
 
 template <bool HILO>

@@ -136,6 +136,7 @@ struct KmAssignArgs {
   long long *acc;
   KmState *state;
   int incremental;     // 1: move only re-labelled points; 0: add every point (acc S zeroed)
+  int all_push;        // small-d path: every point will be accumulated in this pass (labels all -1, or full-update mode)
   int exact_inertia;
   int sm_count;
   int max_smem_optin;
