@@ -99,6 +99,8 @@ struct KmSmallParams {
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
   int64_t chunk;       // points per chunk (multiple of 4); block b walks chunks b, b + grid, ...
   int64_t nchunks;
+  int64_t n_big;       // cell-sorted store: units [0, n_big) have `chunk` points, the rest `chunk_small` (the tail of the pass, for balance)
+  int64_t chunk_small;
   float tau2;          // absolute error term of the filter for this instantiation (hi or hi/lo)
   float cboundf;       // the bound on max|c| itself
   KmPass ps;           // sums / centroids / deltas this pass reads and writes
@@ -285,8 +287,10 @@ __global__ void __launch_bounds__(KM_GRID_THREADS) km_prune_grid_kernel(const Km
   const float prune_M = cboundf + pr.absmax;
   const float margin = 1e-5f * prune_M * prune_M;
   const int lane = threadIdx.x & 31;
-  const int cell = blockIdx.x * (KM_GRID_THREADS / 32) + (threadIdx.x >> 5);
-  if (cell < pr.gp * pr.gp) {
+  // one resident wave of blocks: every warp walks its share of the cells (the prologue above — dependent global
+  // loads and a division — is paid once per block, not once per 16 cells)
+  const int nwarps = gridDim.x * (KM_GRID_THREADS / 32);
+  for (int cell = blockIdx.x * (KM_GRID_THREADS / 32) + (threadIdx.x >> 5); cell < pr.gp * pr.gp; cell += nwarps) {
     const unsigned long long w = km_prune_cell_word(gk_ncf, 2, k, cell, pr, margin, lane);
     if (lane == 0) cells_g[cell] = w;
   }
@@ -475,7 +479,11 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   };
   int64_t ch = blockIdx.x, ch_next = (int64_t)blockIdx.x + gridDim.x;
   if (WQ) { ch = grab(); ch_next = grab(); }
-  auto chunk_len = [&](int64_t c) { return (int)max((int64_t)0, min(p.n - c * p.chunk, p.chunk)); };
+  auto unit_start = [&](int64_t c) -> int64_t { return (WQ && c >= p.n_big) ? p.n_big * p.chunk + (c - p.n_big) * p.chunk_small : c * p.chunk; };
+  auto chunk_len = [&](int64_t c) {
+    const int64_t len = (WQ && c >= p.n_big) ? p.chunk_small : p.chunk;
+    return (int)max((int64_t)0, min(p.n - unit_start(c), len));
+  };
   // block 0 owes the host the pending pass's inertia: its terms first, while no register is live
   __shared__ long long s_g[KM_SMALL_THREADS / 32][2];   // per-warp shares of those terms
   if (blockIdx.x == 0 && ps.D_in != nullptr && ps.slot != nullptr)
@@ -484,7 +492,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   // first round's loads go out before anything else so they fly during the prologue
   KmBatch<D> cur;
   constexpr bool EARLY_LABELS = true;     // labels travel with their points, a round ahead
-  km_load_batch<D, EARLY_LABELS, WQ>(cur, p.x + ch * p.chunk * D, p.labels + ch * p.chunk, 0, chunk_len(ch));
+  km_load_batch<D, EARLY_LABELS, WQ>(cur, p.x + unit_start(ch) * D, p.labels + unit_start(ch), 0, chunk_len(ch));
 
   // ---- prologue = the previous pass's centroid update (a4), redone by every block:
   //   sums      S = S_in (+ D_in when a pass is pending; = D_in in full mode)
@@ -600,8 +608,8 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
 
   while (ch < p.nchunks) {
   const int cn = chunk_len(ch);
-  const float *__restrict__ xb = p.x + ch * p.chunk * D;
-  int32_t *__restrict__ lb = p.labels + ch * p.chunk;
+  const float *__restrict__ xb = p.x + unit_start(ch) * D;
+  int32_t *__restrict__ lb = p.labels + unit_start(ch);
   for (int r0 = 0; r0 < cn; r0 += per_round) {
     // software pipeline: the next round's loads (the next chunk's first, at the end of this
     // one) are in flight during this round's arithmetic
@@ -610,7 +618,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     if (r0 + per_round < cn) {
       km_load_batch<D, EARLY_LABELS, WQ>(nxt, xb, lb, r0 + per_round, cn);
     } else if (ch_next < p.nchunks) {
-      km_load_batch<D, EARLY_LABELS, WQ>(nxt, p.x + ch_next * p.chunk * D, p.labels + ch_next * p.chunk, 0, chunk_len(ch_next));
+      km_load_batch<D, EARLY_LABELS, WQ>(nxt, p.x + unit_start(ch_next) * D, p.labels + unit_start(ch_next), 0, chunk_len(ch_next));
     }
 
     // ---- binary32 filter, top-2 on integer keys
@@ -983,15 +991,25 @@ static cudaError_t launch_small_ap(const KmAssignArgs &a, int64_t *launches) {
   int grid = (int)grid64;
   p.chunk = chunk;
   p.nchunks = grid64;
+  p.n_big = grid64;
+  p.chunk_small = chunk;
   p.work_counter = a.work_counter;
   if (SORTED) {
     // units of 16 warp-rounds (2048 points at d = 2), taken dynamically by the warps of one resident wave
     const int64_t unit = (int64_t)32 * KmSmallCfg<D>::PPT * 16;
     p.chunk = unit;
-    p.nchunks = (a.n + unit - 1) / unit;
-    const int64_t warps_wanted = p.nchunks < 1 ? 1 : p.nchunks;
+    const int64_t nunits = (a.n + unit - 1) / unit;
+    const int64_t warps_wanted = nunits < 1 ? 1 : nunits;
     const int64_t blocks_wanted = (warps_wanted + KM_SMALL_THREADS / 32 - 1) / (KM_SMALL_THREADS / 32);
     grid = (int)(blocks_wanted < cap ? blocks_wanted : cap);
+    // guided: the last unit's worth of points per warp goes out in units of two warp-rounds, so that the warps
+    // finish within a few hundred points of each other (at 13 units per warp a whole unit of slack is 8 % of the pass)
+    const int64_t warps = (int64_t)grid * (KM_SMALL_THREADS / 32);
+    int64_t tail_units = warps < nunits / 2 ? warps : nunits / 2;
+    p.n_big = nunits - tail_units;
+    p.chunk_small = unit / 8;
+    const int64_t rest = a.n - p.n_big * unit;
+    p.nchunks = p.n_big + (rest > 0 ? (rest + p.chunk_small - 1) / p.chunk_small : 0);
   }
   p.scale_a = a.scale_a;
   p.scale_b = a.scale_b;
@@ -1000,7 +1018,8 @@ static cudaError_t launch_small_ap(const KmAssignArgs &a, int64_t *launches) {
   if (PRUNE && p.sorted && a.n > 0) {
     // this pass's candidate words, for every cell, in front of the assignment kernel
     const int cellsn = a.pr.gp * a.pr.gp;
-    km_prune_grid_kernel<<<(cellsn + KM_GRID_THREADS / 32 - 1) / (KM_GRID_THREADS / 32), KM_GRID_THREADS,
+    const int gblocks = (cellsn + KM_GRID_THREADS / 32 - 1) / (KM_GRID_THREADS / 32);
+    km_prune_grid_kernel<<<gblocks < 2 * a.sm_count ? gblocks : 2 * a.sm_count, KM_GRID_THREADS,
                            (size_t)a.k * 2 * sizeof(float), a.stream>>>(a.ps, a.k, a.pr, p.cboundf, a.cells_g, p.work_counter);
     (*launches)++;
   }
