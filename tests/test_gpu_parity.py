@@ -623,7 +623,9 @@ def test_pruned_attached_points_stay_unsorted(km):
 @pytest.mark.parametrize("mode", [0, 1], ids=["incremental", "full"])
 @pytest.mark.parametrize("shape", [(3000, 32, 16, 16), (1500, 128, 8, 32), (20000, 64, 40, 200), (4099, 32, 3, 129),
                                    (9000, 96, 500, 1024), (257, 128, 2, 2), (6000, 16, 12, 40), (5003, 24, 9, 130),
-                                   (3001, 9, 5, 17), (2500, 77, 6, 300), (70000, 48, 64, 64)],
+                                   (3001, 9, 5, 17), (2500, 77, 6, 300), (70000, 48, 64, 64),
+                                   # rows without spare columns: h rides in the extra no-swizzle K-step (d = 49..64, 113..128)
+                                   (2500, 120, 5, 140), (3000, 50, 7, 130), (1031, 113, 3, 300), (777, 64, 4, 129)],
                          ids=lambda s: "n%d_d%d_kt%d_k%d" % s)
 def test_tensor_path_matches_oracle(km, shape, mode):
     n, d, k_true, k = shape

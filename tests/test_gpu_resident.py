@@ -77,6 +77,12 @@ def test_resident_state_carries_on_stepwise(km):
 
 
 @gpu
+def test_comm_info_single_rank(km):
+    with km.KMeansState() as st:
+        assert st.comm_info() == (0, 1, 0)
+
+
+@gpu
 def test_resident_ties_empty_clusters_and_max_iter(km):
     # exact ties (lowest index wins), a centroid nobody picks (keeps its place), max_iter = 1
     x = np.array([[0, 0], [2, 0], [1, 0], [1, 0], [10, 10]], dtype=np.float32)
