@@ -1,4 +1,4 @@
-timeout 300 python bench.py --workload c5 --n-total 125000000 --steps 20 --warmup 3 --shapes none --e2e-steps 1 --run-iters 5 --cpu-seconds 1 > gpurun_out/bs.json 2>gpurun_out/bs.err; echo rc=$?
+timeout 300 python bench.py --workload c5 --n-total 125000000 --steps 20 --warmup 3 --shapes none --e2e-steps 1 --run-iters 5 --cpu-seconds 1 $SHARD_EXTRA > gpurun_out/bs.json 2>gpurun_out/bs.err; echo rc=$?
 python -c "
 import json
 l=json.loads(open('gpurun_out/bs.json').read().strip().splitlines()[-1])
