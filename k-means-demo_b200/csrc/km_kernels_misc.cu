@@ -175,8 +175,9 @@ __global__ void __launch_bounds__(256) km_finalize_grid_kernel(const KmFinalizeA
 
 cudaError_t km_launch_finalize(const KmFinalizeArgs &f, cudaStream_t s, int64_t *launches) {
   int64_t kd = (int64_t)f.k * f.d;
-  if (kd > 16384) {   // large tables: spread the divisions over many blocks
-    int grid = (int)((kd + 256 * 4 - 1) / (256 * 4));
+  if (kd > 1024) {   // more than one block's worth: spread the divisions (128-bit fixed point -> binary64, a double-double
+                     // inertia term each: ~300 instructions per element) over many SMs — one block took 27 us at k*d = 8192
+    int grid = (int)((kd + 255) / 256);
     if (grid > 148) grid = 148;
     km_finalize_grid_kernel<<<grid, 256, 0, s>>>(f);
   } else {
