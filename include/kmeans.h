@@ -120,8 +120,9 @@ KM_API km_status km_comm_unique_id(void *out128);
 KM_API km_status km_comm_init(km_ctx *ctx, const void *id128, int32_t rank, int32_t world);
 /* how the per-iteration sum travels.  km_comm_init also tries to map one small region of every
  * peer (CUDA IPC; all ranks on one node with peer access).  Where that worked on every rank, the
- * small-d path's tables of up to 64 KB (2kd + k + 4 int64) are summed by one small kernel over peer
- * memory instead of an NCCL all-reduce (same integers, same bits); with it, km_set_centroids,
+ * per-iteration table (2kd + k + 4 int64) is summed by one small kernel over peer memory instead of an
+ * NCCL all-reduce (same integers, same bits) — up to 64 KB on the small-d path, up to 896 KB on the
+ * direct and tensor paths; larger tables stay on NCCL.  With it, km_set_centroids,
  * km_reset_labels and km_set_update_mode are collective too (they end with a barrier across the
  * ranks), and a rank that waits more than two minutes for a peer returns KM_ERR_NCCL.
  * *peer_allreduce: 0 = NCCL only, 1 = peer regions mapped, 2 = the tables now installed use them.

@@ -500,8 +500,8 @@ static km_status peer_setup(km_ctx *ctx) {
   if (ctx->world < 2 || ctx->world > KM_PEER_MAX_WORLD) return KM_OK;
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle travels as 8 int64");
   const int W = ctx->world, NH = 9;  // 8 words of handle + "this rank is fine so far"
-  const size_t alloc_bytes = 2u << 20;  // a whole allocation block of its own, so the handle maps exactly this pointer
-  static_assert(KM_PEER_REGION_BYTES <= (2u << 20), "region fits its allocation");
+  const size_t alloc_bytes = KM_PEER_REGION_BYTES;  // 2 MB: a whole allocation block of its own, so the handle maps exactly this pointer
+  static_assert(KM_PEER_SNAP_OFF + 2 * KM_PEER_SNAP_BYTES <= KM_PEER_REGION_BYTES, "the snapshots fit the region");
   bool ok = true;
   void *base = nullptr;
   ok = cudaMalloc(&base, alloc_bytes) == cudaSuccess && cudaMemset(base, 0, alloc_bytes) == cudaSuccess &&
@@ -562,8 +562,8 @@ static km_status peer_setup(km_ctx *ctx) {
 static km_status peer_barrier(km_ctx *ctx) {
   if (!ctx->peer_ok) return KM_OK;
   ctx->peer_epoch++;
-  KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, 0, 0, ctx->peer_epoch, nullptr, ctx->peer_err,
-                                        ctx->stream, &ctx->launches));
+  KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, 0, KM_PEER_FLAGS_OFF, 0, ctx->peer_epoch, nullptr,
+                                        ctx->peer_err, ctx->sm_count, ctx->stream, &ctx->launches));
   return KM_OK;
 }
 
@@ -637,7 +637,8 @@ extern "C" km_status km_comm_info(const km_ctx *ctx, int32_t *rank, int32_t *wor
   if (!ctx) return KM_ERR_INVALID_ARG;
   if (rank) *rank = ctx->rank;
   if (world) *world = ctx->world;
-  if (peer_allreduce) *peer_allreduce = !ctx->peer_ok ? 0 : (ctx->p1D_in_peer ? 2 : 1);
+  const bool acc_peer = ctx->have_centroids && !ctx->p1 && ctx->world > 1 && (size_t)ctx->acc_len * sizeof(long long) <= KM_PEER_SNAP_BYTES;
+  if (peer_allreduce) *peer_allreduce = !ctx->peer_ok ? 0 : ((ctx->p1D_in_peer || acc_peer) ? 2 : 1);
   return KM_OK;
 }
 
@@ -1112,7 +1113,17 @@ static km_status enqueue_pass(km_ctx *ctx, int do_stats, int do_update, int need
     ctx->prof_n++;
   }
   ctx->labels_fresh = false;
-  if (ctx->world > 1)
+  if (ctx->world > 1 && ctx->peer_ok && (size_t)ctx->acc_len * sizeof(long long) <= KM_PEER_SNAP_BYTES) {
+    // the sum across ranks over peer memory (km_peer.cu): this rank's running table is copied into one of two
+    // alternating snapshots inside the region its peers have mapped (the table itself keeps changing — the next
+    // pass, the finalize kernel's scalars — while a slower peer may still be reading), then one kernel does the rest
+    const unsigned long long e = ++ctx->peer_epoch2;
+    const size_t off = KM_PEER_SNAP_OFF + (size_t)(e & 1) * KM_PEER_SNAP_BYTES;
+    KM_CUDA(ctx, cudaMemcpyAsync(static_cast<unsigned char *>(ctx->peer_base[ctx->rank]) + off, ctx->acc,
+                                 (size_t)ctx->acc_len * sizeof(long long), cudaMemcpyDeviceToDevice, ctx->stream));
+    KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, off, KM_PEER_FLAGS2_OFF, ctx->acc_len, e,
+                                          ctx->acc_global, ctx->peer_err, ctx->sm_count, ctx->stream, &ctx->launches));
+  } else if (ctx->world > 1)
     KM_NCCL(ctx, g_nccl.all_reduce(ctx->acc, ctx->acc_global, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
                                    ctx->nccl_comm, ctx->stream));
   KM_CUDA(ctx, km_launch_finalize(make_fin(ctx, slot, do_stats, do_update, needs_change), ctx->stream, &ctx->launches));
@@ -1159,8 +1170,8 @@ static km_status p1_launch(km_ctx *ctx, bool assign, int update, int nc) {
     if (ctx->p1D_in_peer) {  // the one collective of an iteration: one small kernel over peer memory
       ctx->peer_epoch++;
       KM_CUDA(ctx, km_launch_peer_allreduce(ctx->peer_base, ctx->world, ctx->rank, (size_t)ctx->p1_dw * KM_PEER_TABLE_BYTES,
-                                            ctx->acc_len, ctx->peer_epoch, ctx->p1R[ctx->p1_dw], ctx->peer_err, ctx->stream,
-                                            &ctx->launches));
+                                            KM_PEER_FLAGS_OFF, ctx->acc_len, ctx->peer_epoch, ctx->p1R[ctx->p1_dw], ctx->peer_err,
+                                            ctx->sm_count, ctx->stream, &ctx->launches));
     } else if (ctx->world > 1)  // ... or NCCL, in place
       KM_NCCL(ctx, g_nccl.all_reduce(ps.D_out, ps.D_out, (size_t)ctx->acc_len, KM_NCCL_INT64, KM_NCCL_SUM,
                                      ctx->nccl_comm, ctx->stream));

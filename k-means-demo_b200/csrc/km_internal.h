@@ -12,7 +12,12 @@
 #define KM_PEER_MAX_WORLD 16
 #define KM_PEER_TABLE_BYTES (64 * 1024)
 #define KM_PEER_FLAGS_OFF (3 * KM_PEER_TABLE_BYTES)
-#define KM_PEER_REGION_BYTES (KM_PEER_FLAGS_OFF + 4096)
+#define KM_PEER_REGION_BYTES (2u << 20)
+// general path (direct / tensor kernels): two alternating snapshots of this rank's running table, copied in before
+// each sum across ranks; their epoch flags sit 128 bytes after the small-d path's
+#define KM_PEER_FLAGS2_OFF (KM_PEER_FLAGS_OFF + 128)
+#define KM_PEER_SNAP_OFF (KM_PEER_FLAGS_OFF + 4096)
+#define KM_PEER_SNAP_BYTES (896 * 1024)
 #define KM_RING 8      // stats slots in pinned host memory
 #define KM_RUN_LAG 2   // iterations km_run keeps in flight ahead of the host's check
 #define KM_PROF_RING 256  // assign-kernel event pairs kept when km_config.profile_kernels is set
@@ -101,6 +106,7 @@ struct km_ctx {
   bool p1D_in_peer = false;         // p1D[] point into peer_base[rank] (not separately allocated)
   long long *p1R[3] = {nullptr, nullptr, nullptr};  // the summed tables the next pass reads
   unsigned long long peer_epoch = 0;
+  unsigned long long peer_epoch2 = 0;  // ... of the general path's snapshots
   int *peer_err = nullptr;          // mapped pinned host word: a peer never arrived
 
   // ---- tensor path scratch
@@ -178,8 +184,8 @@ bool km_small_prune_setup(int32_t d, int32_t k, int64_t n_local, int64_t min_poi
                           int fine, KmPrune2 *out);
 cudaError_t km_narrow_labels(const int32_t *labels, const unsigned *perm, int64_t n, unsigned char *out_dev, int sm_count,
                              cudaStream_t s, int64_t *launches);
-cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, int64_t len,
-                                     unsigned long long epoch, long long *out, int *err, cudaStream_t s, int64_t *launches);
+cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, size_t flags_off, int64_t len,
+                                     unsigned long long epoch, long long *out, int *err, int sm_count, cudaStream_t s, int64_t *launches);
 // km_resident.cu: the whole km_run loop in one cooperative launch for jobs that fit in shared memory
 #define KM_RESIDENT_MAX_KD 32    // binary64 argmin over all k, no filter: only worth it while k * d is small
 struct KmResidentArgs {

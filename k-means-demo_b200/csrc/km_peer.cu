@@ -37,6 +37,7 @@ struct KmPeerArgs {
   unsigned char *base[KM_PEER_MAX_WORLD];   // every rank's region as mapped HERE (base[rank] = own)
   int world, rank;
   size_t table_off;                          // byte offset of this pass's table inside a region
+  size_t flags_off;                          // ... and of the epoch flags this sum uses
   int64_t len;                               // int64 entries
   unsigned long long epoch;
   long long *out;                            // local: the summed table
@@ -56,9 +57,9 @@ __device__ __forceinline__ unsigned long long global_ns() {
 #define KM_PEER_TIMEOUT_NS 120000000000ULL
 __global__ void __launch_bounds__(KM_PEER_THREADS) km_peer_allreduce_kernel(const KmPeerArgs a) {
   if (blockIdx.x == 0 && (int)threadIdx.x < a.world)   // thread r tells rank r
-    fence_then_st_sys(reinterpret_cast<unsigned long long *>(a.base[threadIdx.x] + KM_PEER_FLAGS_OFF) + a.rank, a.epoch);
+    fence_then_st_sys(reinterpret_cast<unsigned long long *>(a.base[threadIdx.x] + a.flags_off) + a.rank, a.epoch);
   if ((int)threadIdx.x < a.world) {
-    const unsigned long long *f = reinterpret_cast<const unsigned long long *>(a.base[a.rank] + KM_PEER_FLAGS_OFF) + threadIdx.x;
+    const unsigned long long *f = reinterpret_cast<const unsigned long long *>(a.base[a.rank] + a.flags_off) + threadIdx.x;
     const unsigned long long t0 = global_ns();
     while (ld_acquire_sys(f) < a.epoch) {
       __nanosleep(32);
@@ -75,13 +76,14 @@ __global__ void __launch_bounds__(KM_PEER_THREADS) km_peer_allreduce_kernel(cons
 }
 
 // len == 0 is a barrier: every rank has finished reading every table of the epochs before.
-cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, int64_t len,
-                                     unsigned long long epoch, long long *out, int *err, cudaStream_t s, int64_t *launches) {
+cudaError_t km_launch_peer_allreduce(void *const *bases, int world, int rank, size_t table_off, size_t flags_off, int64_t len,
+                                     unsigned long long epoch, long long *out, int *err, int sm_count, cudaStream_t s, int64_t *launches) {
   KmPeerArgs a;
   for (int r = 0; r < KM_PEER_MAX_WORLD; r++) a.base[r] = r < world ? static_cast<unsigned char *>(bases[r]) : nullptr;
-  a.world = world; a.rank = rank; a.table_off = table_off; a.len = len; a.epoch = epoch; a.out = out; a.err = err;
+  a.world = world; a.rank = rank; a.table_off = table_off; a.flags_off = flags_off; a.len = len; a.epoch = epoch; a.out = out; a.err = err;
   int blocks = (int)((len + KM_PEER_THREADS - 1) / KM_PEER_THREADS);
-  blocks = blocks < 1 ? 1 : (blocks > 8 ? 8 : blocks);
+  const int cap = sm_count > 8 ? sm_count / 2 : 8;   // every block polls the flags by itself: all of them must be resident
+  blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
   km_peer_allreduce_kernel<<<blocks, KM_PEER_THREADS, 0, s>>>(a);
   (*launches)++;
   return cudaGetLastError();
