@@ -1444,7 +1444,16 @@ extern "C" km_status km_get_labels_u8(km_ctx *ctx, uint8_t *out, int64_t n) {
     KM_CUDA(ctx, cudaMalloc(&ctx->narrow_buf, (size_t)n));
     ctx->narrow_n = n;
   }
-  KM_CUDA(ctx, km_narrow_labels(ctx->labels, ctx->perm, n, ctx->narrow_buf, ctx->sm_count, ctx->stream, &ctx->launches));
+  const int32_t *src = ctx->labels;
+  if (ctx->perm) {
+    // cell-sorted store: back to the caller's order as int32 first (a scatter of whole words; scattering single bytes
+    // into shared sectors is several times slower), then narrow with coalesced reads and writes
+    if (!ctx->unperm_buf) KM_CUDA(ctx, cudaMalloc(&ctx->unperm_buf, (size_t)n * sizeof(int32_t)));
+    int32_t *tmp = reinterpret_cast<int32_t *>(ctx->unperm_buf);
+    KM_CUDA(ctx, km_unpermute_labels(ctx->labels, ctx->perm, n, tmp, ctx->sm_count, ctx->stream, &ctx->launches));
+    src = tmp;
+  }
+  KM_CUDA(ctx, km_narrow_labels(src, nullptr, n, ctx->narrow_buf, ctx->sm_count, ctx->stream, &ctx->launches));
   return copy_d2h(ctx, out, ctx->narrow_buf, (size_t)n);
 }
 
