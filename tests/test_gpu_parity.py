@@ -647,7 +647,7 @@ def test_tensor_path_matches_oracle(km, shape, mode):
 
 def test_tensor_path_near_ties_and_duplicates(km):
     # many centroids per blob (k >> k_true) makes within-blob near-ties the common case, the
-    # regime where the TF32 stage cannot decide and the exact stage must; plus exact duplicates
+    # regime where the BF16 coarse stage cannot decide and the exact stage must; plus exact duplicates
     rng = np.random.default_rng(3)
     x = oracle.gen_blobs(91, 6000, 64, 4)
     c0 = oracle.forgy_init(x, 96, 4)
