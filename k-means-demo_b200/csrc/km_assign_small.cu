@@ -94,6 +94,7 @@ struct KmSmallParams {
   int incremental;
   int exact_inertia;
   int tab_in_smem;
+  int ntab;            // tables in shared memory: 1 per block, or one per warp (passes that accumulate every point)
   unsigned key_mask;   // low bits of the distance key that hold the centroid index
   float rho2;          // relative part of the ambiguity threshold (carries the 2.5x margin)
   double scale_a, scale_b;  // fixed-point scales of the sums (constant per upload)
@@ -453,7 +454,7 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   // PRUNE: candidate word per cell — in shared memory, built by this block (points in the caller's order),
   // or in global memory, built once per pass by km_prune_grid_kernel (cell-sorted store: a warp stays in
   // one cell for thousands of points and reads its word through L1)
-  unsigned long long *cells_sm = reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal : 0));
+  unsigned long long *cells_sm = reinterpret_cast<unsigned long long *>(stab + (p.tab_in_smem ? L.scal * p.ntab : 0));
   constexpr bool cells_in_smem = PRUNE && !SORTED;
   const unsigned long long *cells = cells_in_smem ? cells_sm : p.cells_g;
   // per-warp queue of points whose sums must move (x, from, to): filled by ballot, drained 32
@@ -527,8 +528,10 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
   const bool publish = blockIdx.x == 0 && pend && ps.slot != nullptr;
   KmBlockTab T;
   T.L = L;
-  T.tab = p.tab_in_smem ? stab : ps.D_out;
-  if (p.tab_in_smem) km_tab_zero(stab, L.scal);
+  // a table per warp where the launcher found room (ALLPUSH passes on an unsorted store: every lane moves a point to
+  // its own cluster, and a shared table would take 512 threads' compare-and-swap loops on a few hundred entries)
+  T.tab = p.tab_in_smem ? stab + (size_t)(p.ntab > 1 ? (threadIdx.x >> 5) : 0) * L.scal : ps.D_out;
+  if (p.tab_in_smem) km_tab_zero(stab, L.scal * p.ntab);
   if (blockIdx.x == 0) {
     if (ps.D_zero)
       for (int e = threadIdx.x; e < (int)L.len; e += KM_SMALL_THREADS) ps.D_zero[e] = 0;
@@ -924,7 +927,15 @@ __global__ void __launch_bounds__(KM_SMALL_THREADS, 2) km_assign_small_kernel(co
     }
   }
   __syncthreads();
-  if (p.tab_in_smem) km_tab_flush(stab, ps.D_out, L.scal);
+  if (p.tab_in_smem) {
+    if (p.ntab == 1) km_tab_flush(stab, ps.D_out, L.scal);
+    else
+      for (int64_t e = threadIdx.x; e < L.scal; e += KM_SMALL_THREADS) {
+        long long v = 0;
+        for (int w = 0; w < p.ntab; w++) v += stab[(size_t)w * L.scal + e];
+        if (v != 0) km_atomic_add_ll(ps.D_out + e, v);
+      }
+  }
   if (threadIdx.x < KM_ACC_SCALARS && s_scal[threadIdx.x] != 0)
     km_atomic_add_ll(ps.D_out + L.scal + threadIdx.x, s_scal[threadIdx.x]);
 }
@@ -968,6 +979,11 @@ static cudaError_t launch_small_ap(const KmAssignArgs &a, int64_t *launches) {
     if (!p.sorted) smem += (size_t)a.pr.gp * a.pr.gp * sizeof(unsigned long long);   // the block builds its own copy
   }
   smem += (size_t)(KM_SMALL_THREADS / 32) * 64 * (D + 2) * sizeof(unsigned);   // per-warp move queues
+  p.ntab = 1;
+  if (ALLPUSH && p.tab_in_smem && smem + (KM_SMALL_THREADS / 32 - 1) * tab_bytes + 4096 <= (size_t)a.max_smem_optin / 2) {
+    p.ntab = KM_SMALL_THREADS / 32;   // a table per warp
+    smem += (KM_SMALL_THREADS / 32 - 1) * tab_bytes;
+  }
   auto kern = km_assign_small_kernel<D, HILO, PRUNE, SORTED, ALLPUSH>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
