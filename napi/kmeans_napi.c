@@ -143,7 +143,7 @@ static napi_value Run(napi_env env, napi_callback_info info) {
   return km_stats_object(env, &s);
 }
 
-/* labels(state, out: Int32Array), centroids(state, out: Float64Array), counts(state, out: BigInt64Array) */
+/* labels(state, out: Int32Array | Uint8Array), centroids(state, out: Float64Array), counts(state, out: BigInt64Array) */
 static napi_value km_copy_out(napi_env env, napi_callback_info info, int what) {
   size_t argc = 2;
   napi_value argv[KM_NAPI_MAX_ARGS];
@@ -168,6 +168,7 @@ static napi_value km_copy_out(napi_env env, napi_callback_info info, int what) {
     return NULL;
   }
   if (what == 0 && ty == napi_int32_array) st = km_get_labels(ctx, (int32_t *)out, n_local);
+  else if (what == 0 && ty == napi_uint8_array) st = km_get_labels_u8(ctx, (uint8_t *)out, n_local);   /* k <= 255: a byte per label */
   else if (what == 1 && ty == napi_float64_array) st = km_get_centroids(ctx, (double *)out);
   else if (what == 2 && ty == napi_bigint64_array) st = km_get_counts(ctx, (int64_t *)out);
   else { napi_throw_error(env, "ERR_KMEANS", "output array has the wrong element type"); return NULL; }
